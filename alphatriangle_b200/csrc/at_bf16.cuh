@@ -1,0 +1,21 @@
+// tcgen05 / TMEM bf16 path (at_bf16.cu): interface towards the engine.
+#pragma once
+
+#include <string>
+
+#include "at_engine.cuh"
+
+namespace at {
+
+struct Bf16Path;  // opaque: packed bf16 weight sets + scratch of the tcgen05 kernels
+
+// Creates the path if the plan matches what the kernels specialise; otherwise
+// leaves *out null, explains why in *reason and still returns AT_OK.
+int bf16_create(const Plan& plan, int64_t max_batch, Bf16Path** out, std::string* reason);
+void bf16_destroy(Bf16Path* p);
+// folded fp32 set -> bf16 operand images for weight set `slot` (0/1)
+int bf16_pack_weights(Bf16Path* p, const Plan& plan, const float* d_folded, int slot, cudaStream_t stream);
+int bf16_evaluate(Bf16Path* p, const Plan& plan, const float* d_folded, int slot, const void* d_states, int64_t batch, float* d_policy,
+                  float* d_value, uint32_t* d_flags, cudaStream_t stream, int64_t* launches);
+
+}  // namespace at

@@ -1,0 +1,191 @@
+// Feature extraction: PackedState[B] -> grid f32 [B,Cg,R,C] + other f32 [B,D].
+//
+// Restates, per state, alphatriangle/features/extractor.py:33-147 and
+// alphatriangle/features/grid_features.py:7-42. The reference evaluates every
+// "other" feature in float64 (Python floats / numpy float64 scalars) and rounds
+// once when the value is stored into a float32 array, so the kernel does the same
+// operations in the same order with explicitly rounded fp64 intrinsics (no FMA
+// contraction) and one __double2float_rn per feature. Result: bit-exact.
+//
+// HBM-bound: 80 B in + (Cg*R*C + D)*4 B out per state (680 B at the defaults).
+// One block = 16 states; 16 lanes cooperate on a state's columns, then the whole
+// block streams the 16 states' outputs with fully coalesced stores.
+
+#include "at_common.cuh"
+
+namespace at {
+
+namespace {
+
+constexpr int kThreads = 256;
+constexpr int kLanesPerState = 16;
+constexpr int kStatesPerBlock = kThreads / kLanesPerState;
+constexpr int kMaxOther = AT_MAX_SLOTS * 8 + 6;  // slots*7 + slots + 6
+
+__device__ __forceinline__ bool bit_at(const uint32_t* m, int i) { return (m[i >> 5] >> (i & 31)) & 1u; }
+
+__device__ __forceinline__ double clip_d(double x, double lo, double hi) {
+  // np.clip on a float64 scalar: NaN propagates, otherwise min(max(x, lo), hi)
+  if (x != x) return x;
+  return fmin(fmax(x, lo), hi);
+}
+
+__device__ __forceinline__ float store_f32(double v) {
+  // value assigned into a float32 ndarray, then nan_to_num(nan=0, posinf=0, neginf=0)
+  float f = __double2float_rn(v);
+  return is_finite_f(f) ? f : 0.0f;
+}
+
+__global__ void __launch_bounds__(kThreads) features_kernel(const PackedState* __restrict__ states, int64_t batch, int rows, int cols,
+                                                           int slots, int grid_channels, int other_dim,
+                                                           float* __restrict__ grid, float* __restrict__ other) {
+  __shared__ PackedState s_state[kStatesPerBlock];
+  __shared__ int s_height[kStatesPerBlock][AT_MAX_CELLS];
+  __shared__ float s_other[kStatesPerBlock][kMaxOther];
+
+  const int tid = threadIdx.x;
+  const int64_t first = (int64_t)blockIdx.x * kStatesPerBlock;
+  const int n_here = (int)min((int64_t)kStatesPerBlock, batch - first);
+
+  // stage the packed records (16-byte coalesced loads)
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(states + first);
+    uint4* dst = reinterpret_cast<uint4*>(s_state);
+    const int n_vec = n_here * (AT_STATE_BYTES / 16);
+    for (int i = tid; i < n_vec; i += kThreads) dst[i] = __ldg(src + i);
+  }
+  __syncthreads();
+
+  const int s = tid / kLanesPerState;
+  const int lane = tid % kLanesPerState;
+  const unsigned group_mask = 0xFFFFu << ((tid & 31) & ~15);
+  const int cells = rows * cols;
+  const int n_full = slots * 7 + slots + 6;
+
+  if (s < n_here) {
+    const PackedState& st = s_state[s];
+    // grid_features.get_column_heights / count_holes (grid_features.py:7-33)
+    int sum_h = 0, max_h = 0, holes = 0;
+    for (int c = lane; c < cols; c += kLanesPerState) {
+      int top = -1;
+      for (int r = 0; r < rows; ++r) {
+        const int i = r * cols + c;
+        if (bit_at(st.occ, i) && !bit_at(st.death, i)) top = r;
+      }
+      const int h = top + 1;
+      int empty_below = 0;
+      for (int r = 0; r < h; ++r) {
+        const int i = r * cols + c;
+        if (!bit_at(st.occ, i) && !bit_at(st.death, i)) ++empty_below;
+      }
+      s_height[s][c] = h;
+      sum_h += h;
+      max_h = max(max_h, h);
+      holes += empty_below;
+    }
+    __syncwarp(group_mask);
+    // grid_features.get_bumpiness (grid_features.py:36-42): integer-valued, exact in fp64
+    int bump = 0;
+    for (int c = lane; c + 1 < cols; c += kLanesPerState) bump += abs(s_height[s][c] - s_height[s][c + 1]);
+#pragma unroll
+    for (int off = kLanesPerState / 2; off > 0; off >>= 1) {
+      sum_h += __shfl_xor_sync(group_mask, sum_h, off, kLanesPerState);
+      max_h = max(max_h, __shfl_xor_sync(group_mask, max_h, off, kLanesPerState));
+      holes += __shfl_xor_sync(group_mask, holes, off, kLanesPerState);
+      bump += __shfl_xor_sync(group_mask, bump, off, kLanesPerState);
+    }
+
+    if (lane == 0) {
+      // _get_explicit_features (extractor.py:92-118)
+      int dead = 0;
+      for (int w = 0; w < 4; ++w) {
+        const int lo = w * 32;
+        uint32_t valid = cells >= lo + 32 ? 0xFFFFFFFFu : (cells > lo ? ((1u << (cells - lo)) - 1u) : 0u);
+        dead += __popc(st.death[w] & valid);
+      }
+      const int playable = cells - dead;
+      float* f = &s_other[s][slots * 8];
+      const double drows = (double)rows;
+      f[0] = store_f32(clip_d(__ddiv_rn(st.score, 100.0), -5.0, 5.0));
+      f[1] = store_f32(__ddiv_rn(__ddiv_rn((double)sum_h, (double)cols), drows));  // np.mean(heights) / rows
+      f[2] = store_f32(__ddiv_rn((double)max_h, drows));
+      f[3] = playable > 0 ? store_f32(__ddiv_rn((double)holes, (double)playable)) : 0.0f;
+      f[4] = cols > 1 ? store_f32(__ddiv_rn(__ddiv_rn((double)bump, (double)(cols - 1)), drows)) : 0.0f;
+      f[5] = store_f32(clip_d(__ddiv_rn((double)st.step, 1000.0), 0.0, 1.0));
+    } else if (lane <= slots) {
+      // _get_shape_features / _get_shape_availability (extractor.py:48-90), one lane per slot
+      const int i = lane - 1;
+      const int8_t* sl = st.slot[i];
+      const int present = sl[0] != 0;
+      const int n = (int)(uint8_t)sl[1];
+      float* f = &s_other[s][i * 7];
+      if (present && n > 0) {
+        const int ups = (int)(uint8_t)sl[2];
+        const int min_r = sl[4], min_c = sl[5], max_r = sl[6], max_c = sl[7];
+        const double dn = (double)n;
+        const double drows = (double)rows, dcols = (double)cols;
+        const double width_eff = __dadd_rn(__dmul_rn((double)(max_c - min_c + 1), 0.75), 0.25);
+        f[0] = store_f32(clip_d(__ddiv_rn(dn, 5.0), 0.0, 1.0));
+        f[1] = store_f32(__ddiv_rn((double)ups, dn));
+        f[2] = store_f32(__ddiv_rn((double)(n - ups), dn));
+        f[3] = store_f32(clip_d(__ddiv_rn((double)(max_r - min_r + 1), drows), 0.0, 1.0));
+        f[4] = store_f32(clip_d(__ddiv_rn(width_eff, dcols), 0.0, 1.0));
+        f[5] = store_f32(clip_d(__ddiv_rn(__ddiv_rn((double)(min_r + max_r), 2.0), drows), 0.0, 1.0));
+        f[6] = store_f32(clip_d(__ddiv_rn(__ddiv_rn((double)(min_c + max_c), 2.0), dcols), 0.0, 1.0));
+      } else {
+#pragma unroll
+        for (int k = 0; k < 7; ++k) f[k] = 0.0f;
+      }
+      s_other[s][slots * 7 + i] = present ? 1.0f : 0.0f;
+    }
+  }
+  __syncthreads();
+
+  // other: concat [shape(7*slots), avail(slots), explicit(6)], zero-pad or truncate to D (extractor.py:120-139)
+  {
+    float* dst = other + first * other_dim;
+    const int total = n_here * other_dim;
+    for (int i = tid; i < total; i += kThreads) {
+      const int ss = i / other_dim, d = i - ss * other_dim;
+      dst[i] = d < n_full ? s_other[ss][d] : 0.0f;
+    }
+  }
+  // grid: channel 0 = +1 occupied&~death, -1 death, 0 otherwise; further channels zero (extractor.py:33-46)
+  {
+    const int per = grid_channels * cells;
+    float* dst = grid + first * per;
+    const int total = n_here * per;
+    for (int i = tid; i < total; i += kThreads) {
+      const int ss = i / per, e = i - ss * per;
+      float v = 0.0f;
+      if (e < cells) {
+        const PackedState& st = s_state[ss];
+        v = bit_at(st.death, e) ? -1.0f : (bit_at(st.occ, e) ? 1.0f : 0.0f);
+      }
+      dst[i] = v;
+    }
+  }
+}
+
+}  // namespace
+
+int launch_features(const at_env_desc& env, int grid_channels, int other_dim, const void* d_states, int64_t batch, float* d_grid,
+                    float* d_other, cudaStream_t stream) {
+  if (env.rows <= 0 || env.cols <= 0 || env.rows * env.cols > AT_MAX_CELLS)
+    return fail(AT_E_INVALID, "at_extract_features: need 0 < rows*cols <= 128");
+  if (env.slots <= 0 || env.slots > AT_MAX_SLOTS) return fail(AT_E_INVALID, "at_extract_features: need 1 <= slots <= 4");
+  if (grid_channels <= 0 || other_dim <= 0) return fail(AT_E_INVALID, "at_extract_features: grid_channels and other_dim must be positive");
+  if (batch < 0) return fail(AT_E_INVALID, "at_extract_features: negative batch");
+  if (batch == 0) return AT_OK;
+  if (!d_states || !d_grid || !d_other) return fail(AT_E_INVALID, "at_extract_features: null pointer");
+  if ((reinterpret_cast<uintptr_t>(d_states) & 15u) != 0) return fail(AT_E_INVALID, "at_extract_features: d_states must be 16-byte aligned");
+  const int64_t blocks = (batch + kStatesPerBlock - 1) / kStatesPerBlock;
+  if (blocks > 0x7FFFFFFF) return fail(AT_E_INVALID, "at_extract_features: batch too large");
+  // slot layout inside s_other: shape features at [i*7], availability at [slots*7+i], explicit at [slots*8]
+  features_kernel<<<(unsigned)blocks, kThreads, 0, stream>>>(static_cast<const PackedState*>(d_states), batch, env.rows, env.cols,
+                                                              env.slots, grid_channels, other_dim, d_grid, d_other);
+  AT_CUDA_TRY(cudaGetLastError());
+  return AT_OK;
+}
+
+}  // namespace at

@@ -1,0 +1,176 @@
+"""Python handle on the native engine (at_engine_* in include/at_b200.h).
+
+torch is used here for what the task allows it for: device memory (output
+tensors, pinned staging) and streams. All arithmetic happens inside the library.
+"""
+
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _lib
+from .packing import RECORD_BYTES
+
+
+def _stream_ptr(device: torch.device) -> C.c_void_p:
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
+
+
+def _ptr(t: torch.Tensor) -> C.c_void_p:
+    return C.c_void_p(t.data_ptr())
+
+
+class Engine:
+    def __init__(self, model_config, env_config, device: torch.device, max_batch: int):
+        if device.type != "cuda":
+            raise _lib.LibraryError(
+                f"alphatriangle_b200 evaluates on a B200 only (device={device}); there is no CPU path."
+            )
+        self.lib = _lib.load()
+        self.device = torch.device("cuda", device.index if device.index is not None else torch.cuda.current_device())
+        self.max_batch = int(max_batch)
+        self.desc = _lib.model_desc(model_config, env_config)
+        handle = C.c_void_p()
+        _lib.check(
+            self.lib.at_engine_create(C.byref(self.desc), self.device.index, self.max_batch, C.byref(handle)),
+            "at_engine_create",
+        )
+        self.handle = handle
+        self.action_dim = int(self.lib.at_engine_action_dim(self.handle))
+        self.image_floats = int(self.lib.at_engine_weight_floats(self.handle))
+        self.table = self._read_table()
+        # pinned staging for the host entry point
+        self._h_states = torch.empty((self.max_batch, RECORD_BYTES), dtype=torch.uint8, pin_memory=True)
+        self._h_policy = torch.empty((self.max_batch, self.action_dim), dtype=torch.float32, pin_memory=True)
+        self._h_value = torch.empty((self.max_batch,), dtype=torch.float32, pin_memory=True)
+        self._h_flags = torch.zeros((4,), dtype=torch.int32, pin_memory=True)
+        self._d_flags = torch.zeros((4,), dtype=torch.int32, device=self.device)
+
+    def _read_table(self) -> list[tuple[str, int, int]]:
+        out = []
+        name, off, numel = C.c_char_p(), C.c_int64(), C.c_int64()
+        for i in range(int(self.lib.at_engine_weight_entries(self.handle))):
+            _lib.check(
+                self.lib.at_engine_weight_entry(self.handle, i, C.byref(name), C.byref(off), C.byref(numel)),
+                "at_engine_weight_entry",
+            )
+            out.append((name.value.decode(), int(off.value), int(numel.value)))
+        return out
+
+    def close(self) -> None:
+        if getattr(self, "handle", None):
+            self.lib.at_engine_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):  # pragma: no cover - interpreter teardown order
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- weights -------------------------------------------------------------------
+    def build_image(self, state_dict: dict[str, torch.Tensor]) -> torch.Tensor:
+        """Concatenate the float tensors of a reference-keyed state_dict in engine order (on the device)."""
+        parts = []
+        for name, _off, numel in self.table:
+            if name not in state_dict:
+                raise KeyError(f"state_dict is missing {name!r}")
+            t = state_dict[name]
+            if t.numel() != numel:
+                raise ValueError(f"{name}: expected {numel} elements, got {tuple(t.shape)}")
+            parts.append(t.detach().to(device=self.device, dtype=torch.float32).reshape(-1))
+        return torch.cat(parts) if parts else torch.empty(0, device=self.device)
+
+    def load_image(self, image: torch.Tensor, version: int = 0) -> None:
+        if image.device != self.device or image.dtype != torch.float32 or not image.is_contiguous():
+            raise ValueError("weight image must be a contiguous float32 tensor on the engine's device")
+        _lib.check(
+            self.lib.at_engine_load_weights(self.handle, _ptr(image), image.numel(), int(version), _stream_ptr(self.device)),
+            "at_engine_load_weights",
+        )
+        self._last_image = image  # keep alive until the fold kernels queued on the stream have read it
+
+    def weight_version(self) -> int:
+        return int(self.lib.at_engine_weight_version(self.handle))
+
+    def supports(self, precision: int) -> bool:
+        return bool(self.lib.at_engine_supports(self.handle, precision))
+
+    def last_launches(self) -> int:
+        return int(self.lib.at_engine_last_launches(self.handle))
+
+    # ---- evaluation ------------------------------------------------------------------
+    def forward(self, grid: torch.Tensor, other: torch.Tensor, precision: int = _lib.PREC_FP32):
+        """Prepared features (device, fp32) -> (probs [B,A], value [B], flags int)."""
+        b = grid.shape[0]
+        grid = grid.to(device=self.device, dtype=torch.float32).contiguous()
+        other = other.to(device=self.device, dtype=torch.float32).contiguous()
+        probs = torch.empty((b, self.action_dim), dtype=torch.float32, device=self.device)
+        value = torch.empty((b,), dtype=torch.float32, device=self.device)
+        self._d_flags.zero_()
+        _lib.check(
+            self.lib.at_engine_forward(
+                self.handle, precision, _ptr(grid), _ptr(other), b, _ptr(probs), _ptr(value), _ptr(self._d_flags),
+                _stream_ptr(self.device),
+            ),
+            "at_engine_forward",
+        )
+        return probs, value, int(self._d_flags[0].item())
+
+    def evaluate_packed(self, packed: torch.Tensor, precision: int, probs: torch.Tensor | None = None,
+                        value: torch.Tensor | None = None, flags: torch.Tensor | None = None):
+        """PackedState[B] on the device -> probs / value on the device. Asynchronous (no host sync)."""
+        if packed.device != self.device or packed.dtype != torch.uint8 or packed.dim() != 2 or packed.shape[1] != RECORD_BYTES:
+            raise ValueError("packed must be a uint8 [B,80] tensor on the engine's device")
+        if not packed.is_contiguous():
+            packed = packed.contiguous()
+        b = packed.shape[0]
+        if probs is None:
+            probs = torch.empty((b, self.action_dim), dtype=torch.float32, device=self.device)
+        if value is None:
+            value = torch.empty((b,), dtype=torch.float32, device=self.device)
+        if flags is None:
+            flags = self._d_flags
+            flags.zero_()
+        _lib.check(
+            self.lib.at_engine_evaluate_packed(
+                self.handle, precision, _ptr(packed), b, _ptr(probs), _ptr(value), _ptr(flags), _stream_ptr(self.device)
+            ),
+            "at_engine_evaluate_packed",
+        )
+        return probs, value, flags
+
+    def evaluate_host(self, packed: np.ndarray | torch.Tensor, precision: int):
+        """Host records -> (probs ndarray [B,A], value ndarray [B], flags int); views of pinned staging, valid until the next call."""
+        b = int(packed.shape[0])
+        if b > self.max_batch:
+            raise ValueError(f"batch {b} exceeds max_batch {self.max_batch}")
+        src = packed if isinstance(packed, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(packed))
+        self._h_states[:b].copy_(src)
+        _lib.check(
+            self.lib.at_engine_evaluate_host(
+                self.handle, precision, _ptr(self._h_states), b, _ptr(self._h_policy), _ptr(self._h_value), _ptr(self._h_flags),
+                _stream_ptr(self.device),
+            ),
+            "at_engine_evaluate_host",
+        )
+        return self._h_policy[:b].numpy(), self._h_value[:b].numpy(), int(self._h_flags[0].item())
+
+    def extract_features(self, packed: torch.Tensor, grid_channels: int, other_dim: int):
+        """PackedState[B] on the device -> (grid [B,Cg,R,C], other [B,D]) on the device."""
+        b = packed.shape[0]
+        env = self.desc.env
+        grid = torch.empty((b, grid_channels, env.rows, env.cols), dtype=torch.float32, device=self.device)
+        other = torch.empty((b, other_dim), dtype=torch.float32, device=self.device)
+        if b:
+            _lib.check(
+                self.lib.at_extract_features(
+                    C.byref(self.desc.env), grid_channels, other_dim, _ptr(packed), b, _ptr(grid), _ptr(other),
+                    _stream_ptr(self.device),
+                ),
+                "at_extract_features",
+            )
+        return grid, other

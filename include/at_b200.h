@@ -1,0 +1,160 @@
+/*
+ * at_b200.h -- C ABI of the B200 leaf-evaluation library (libat_b200.so).
+ *
+ * The reference (lguibr/alphatriangle) has no FFI of its own: its boundary for
+ * this path is the duck-typed Python protocol `NeuralNetwork.evaluate_state /
+ * evaluate_batch / get_weights / set_weights` (alphatriangle/nn/network.py:165,
+ * 243,320,325) that trimcts calls. Every entry point below names the reference
+ * code it stands in for. All functions return 0 on success or a negative
+ * AT_E_* code; `at_last_error()` holds the message of the calling thread's last
+ * failure. Nothing here throws, allocates through torch, or takes torch types:
+ * pointers are raw device (d_*) or host (h_*) addresses, `stream` is a
+ * cudaStream_t passed as void* (NULL = the legacy default stream).
+ */
+#ifndef AT_B200_H
+#define AT_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AT_ABI_VERSION 1
+
+/* error codes */
+#define AT_OK 0
+#define AT_E_INVALID (-1)     /* bad argument / unsupported configuration */
+#define AT_E_CUDA (-2)        /* a CUDA runtime call failed */
+#define AT_E_STATE (-3)       /* call order violated (e.g. evaluate before weights were loaded) */
+#define AT_E_UNSUPPORTED (-4) /* valid model, but the requested precision path cannot run it */
+
+/* bits of the per-call status word written by the evaluate entry points; they
+ * map one-to-one onto the reference's isfinite checks (network.py:147-154,
+ * 260-274), which the Python host turns into NetworkEvaluationError. */
+#define AT_FLAG_NONFINITE_GRID 1u
+#define AT_FLAG_NONFINITE_OTHER 2u
+#define AT_FLAG_NONFINITE_POLICY_LOGITS 4u
+#define AT_FLAG_NONFINITE_VALUE_LOGITS 8u
+#define AT_FLAG_NONFINITE_POLICY_PROBS 16u
+
+/* PackedState: 80-byte record, see alphatriangle_b200/packing.py for the field map. */
+#define AT_STATE_BYTES 80
+#define AT_MAX_CELLS 128
+#define AT_MAX_SLOTS 4
+#define AT_MAX_CONVS 8
+#define AT_MAX_MLP 4
+
+enum at_activation { AT_ACT_NONE = 0, AT_ACT_RELU = 1, AT_ACT_GELU = 2, AT_ACT_SILU = 3, AT_ACT_TANH = 4, AT_ACT_SIGMOID = 5 };
+
+/* precision of the forward pass */
+enum at_precision {
+  AT_PREC_FP32 = 0, /* fp32 CUDA-core path, any configuration; parity max-abs 1e-4 */
+  AT_PREC_BF16 = 1  /* tcgen05/TMEM bf16 path, fp32 accumulate; parity policy KL <= 1e-3 */
+};
+
+/* Game geometry: trianglengin.EnvConfig as read at extractor.py:25,39,50. */
+typedef struct at_env_desc {
+  int32_t rows, cols, slots;
+} at_env_desc;
+
+/* Network dimensions: ModelConfig (alphatriangle/config/model_config.py:17-59),
+ * with CONV_* already resolved to integer (kh,kw),(sh,sw),(ph,pw). */
+typedef struct at_model_desc {
+  at_env_desc env;
+  int32_t grid_channels;
+  int32_t n_conv;
+  int32_t conv_filters[AT_MAX_CONVS];
+  int32_t conv_kernel[AT_MAX_CONVS][2];
+  int32_t conv_stride[AT_MAX_CONVS][2];
+  int32_t conv_pad[AT_MAX_CONVS][2];
+  int32_t n_res_blocks;
+  int32_t res_filters;
+  int32_t use_transformer; /* USE_TRANSFORMER && TRANSFORMER_LAYERS > 0 */
+  int32_t t_dim, t_heads, t_layers, t_ff;
+  int32_t n_shared, shared_dims[AT_MAX_MLP];
+  int32_t n_policy, policy_dims[AT_MAX_MLP];
+  int32_t n_value, value_dims[AT_MAX_MLP];
+  int32_t num_atoms;
+  float v_min, v_max;
+  int32_t activation; /* enum at_activation */
+  int32_t use_batch_norm;
+  int32_t other_dim; /* OTHER_NN_INPUT_FEATURES_DIM */
+} at_model_desc;
+
+typedef struct at_engine at_engine; /* opaque */
+
+int at_abi_version(void);
+const char* at_last_error(void);
+
+/* ---- features ---------------------------------------------------------- */
+
+/* extract_state_features for a batch (alphatriangle/features/extractor.py:150-171,
+ * grid_features.py:7-42): PackedState[B] -> grid f32 [B,grid_channels,rows,cols]
+ * and other f32 [B,other_dim] (pad / truncate per extractor.py:127-139). Bit-exact. */
+int at_extract_features(const at_env_desc* env, int grid_channels, int other_dim, const void* d_states, int64_t batch,
+                        float* d_grid, float* d_other, void* stream);
+
+/* ---- engine ------------------------------------------------------------ */
+
+/* NeuralNetwork.__init__ (network.py:40-67): validates the configuration, sizes
+ * the weight image and allocates engine-owned device memory for batches of up to
+ * `max_batch` states on CUDA device `device`. */
+int at_engine_create(const at_model_desc* desc, int device, int64_t max_batch, at_engine** out);
+int at_engine_destroy(at_engine* e);
+
+/* The weight image is every floating-point tensor of the reference state_dict
+ * (network.py:320-323) concatenated as fp32. The table below is the single
+ * source of truth for its order: entry i is the reference key name (e.g.
+ * "res_body.0.conv1.1.running_var"), its float offset and element count. */
+int64_t at_engine_weight_floats(const at_engine* e);
+int at_engine_weight_entries(const at_engine* e);
+int at_engine_weight_entry(const at_engine* e, int index, const char** name, int64_t* offset, int64_t* numel);
+
+/* NeuralNetwork.set_weights (network.py:325-336) for the engine's copy: reads the
+ * fp32 weight image from DEVICE memory (e.g. straight out of an NCCL receive
+ * buffer), folds eval-mode BatchNorm, permutes / casts / tiles for the kernels
+ * into the engine's inactive weight set and makes it the active one once the
+ * work queued on `stream` completes. `version` is an opaque tag (the trainer's
+ * global_step, worker_manager.py:184-187) returned by at_engine_weight_version. */
+int at_engine_load_weights(at_engine* e, const float* d_image, int64_t n_floats, int64_t version, void* stream);
+int64_t at_engine_weight_version(const at_engine* e);
+
+/* 1 if the configuration can run on the tcgen05 bf16 path, else 0 (reason in at_last_error). */
+int at_engine_supports(const at_engine* e, int precision);
+
+/* AlphaTriangleNet.forward + softmax + expected value on prepared feature tensors
+ * (model.py:268-297, network.py:258-278): grid f32 [B,grid_channels,rows,cols]
+ * contiguous, other f32 [B,other_dim] -> policy probs f32 [B,action_dim],
+ * expected value f32 [B]; *d_flags (uint32, device) is OR-ed with AT_FLAG_* bits. */
+int at_engine_forward(at_engine* e, int precision, const float* d_grid, const float* d_other, int64_t batch, float* d_policy,
+                      float* d_value, uint32_t* d_flags, void* stream);
+
+/* NeuralNetwork.evaluate_batch at the tensor boundary (network.py:243-278 without
+ * the Python dict building): PackedState[B] in device memory -> probs, values. */
+int at_engine_evaluate_packed(at_engine* e, int precision, const void* d_states, int64_t batch, float* d_policy, float* d_value,
+                              uint32_t* d_flags, void* stream);
+
+/* Same with HOST buffers (pinned memory recommended): copies the states in,
+ * evaluates, copies probs / values / flags out and waits. This is the call a
+ * host application (trimcts-style batcher) makes. */
+int at_engine_evaluate_host(at_engine* e, int precision, const void* h_states, int64_t batch, float* h_policy, float* h_value,
+                            uint32_t* h_flags, void* stream);
+
+/* Introspection used by bench.py: kernels launched by the last evaluate call. */
+int64_t at_engine_last_launches(const at_engine* e);
+int at_engine_action_dim(const at_engine* e);
+
+/* ---- bring-up probe ------------------------------------------------------ */
+
+/* One 128xN tcgen05.mma chain over K (bf16, fp32 accumulate in TMEM) on operand
+ * images the caller laid out, with the descriptor fields given explicitly.
+ * Test-only: pins the shared-memory descriptor conventions the tower relies on. */
+int at_probe_umma(const void* d_a_image, int64_t a_bytes, const void* d_b_image, int64_t b_bytes, int n, int k,
+                  uint32_t a_start_off, uint32_t a_lbo, uint32_t a_sbo, uint32_t a_kstep, uint32_t b_start_off, uint32_t b_lbo,
+                  uint32_t b_sbo, uint32_t b_kstep, int layout_type, float* d_out /* [128,n] */, uint32_t* d_status, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AT_B200_H */
