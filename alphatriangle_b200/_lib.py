@@ -33,6 +33,7 @@ EXPORTS = (
     "at_abi_version",
     "at_last_error",
     "at_extract_features",
+    "at_model_describe",
     "at_engine_create",
     "at_engine_destroy",
     "at_engine_weight_floats",
@@ -102,6 +103,7 @@ def _bind(lib: C.CDLL) -> None:
         "at_abi_version": (i32, []),
         "at_last_error": (C.c_char_p, []),
         "at_extract_features": (i32, [C.POINTER(EnvDesc), i32, i32, vp, i64, vp, vp, vp]),
+        "at_model_describe": (i64, [C.POINTER(ModelDesc), C.c_char_p, i64]),
         "at_engine_create": (i32, [C.POINTER(ModelDesc), i32, i64, C.POINTER(vp)]),
         "at_engine_destroy": (i32, [vp]),
         "at_engine_weight_floats": (i64, [vp]),
@@ -206,3 +208,19 @@ def model_desc(model_config, env_config) -> ModelDesc:
     d.use_batch_norm = 1 if mc.USE_BATCH_NORM else 0
     d.other_dim = mc.OTHER_NN_INPUT_FEATURES_DIM
     return d
+
+
+def weight_table(model_config, env_config) -> list[tuple[str, int, int]]:
+    """(reference state_dict key, float offset, numel) for every float tensor, in image order. Needs no GPU."""
+    lib = load()
+    d = model_desc(model_config, env_config)
+    need = lib.at_model_describe(C.byref(d), None, 0)
+    if need < 0:
+        raise LibraryError(f"at_model_describe failed ({need}): {last_error()}", int(need))
+    buf = C.create_string_buffer(int(need) + 1)
+    lib.at_model_describe(C.byref(d), buf, need + 1)
+    rows = []
+    for line in buf.value.decode().splitlines():
+        name, off, numel = line.rsplit(" ", 2)
+        rows.append((name, int(off), int(numel)))
+    return rows

@@ -264,6 +264,21 @@ int at_extract_features(const at_env_desc* env, int grid_channels, int other_dim
   return launch_features(*env, grid_channels, other_dim, d_states, batch, d_grid, d_other, static_cast<cudaStream_t>(stream));
 }
 
+int64_t at_model_describe(const at_model_desc* desc, char* buf, int64_t cap) {
+  if (!desc) return fail(AT_E_INVALID, "at_model_describe: null desc");
+  Plan plan;
+  const int rc = build_plan(*desc, plan);
+  if (rc != AT_OK) return rc;
+  std::string text;
+  for (const ImageEntry& en : plan.image) text += en.name + " " + std::to_string(en.offset) + " " + std::to_string(en.numel) + "\n";
+  if (buf && cap > 0) {
+    const int64_t n = (int64_t)text.size() < cap - 1 ? (int64_t)text.size() : cap - 1;
+    std::memcpy(buf, text.data(), (size_t)n);
+    buf[n] = 0;
+  }
+  return (int64_t)text.size();
+}
+
 int at_engine_create(const at_model_desc* desc, int device, int64_t max_batch, at_engine** out) {
   if (!desc || !out) return fail(AT_E_INVALID, "at_engine_create: null argument");
   *out = nullptr;

@@ -95,6 +95,14 @@ const char* at_last_error(void);
 int at_extract_features(const at_env_desc* env, int grid_channels, int other_dim, const void* d_states, int64_t batch,
                         float* d_grid, float* d_other, void* stream);
 
+/* ---- model description (no GPU needed) ---------------------------------- */
+
+/* The weight-image table for a configuration, as text: one line per float tensor of
+ * the reference state_dict (module tree built at alphatriangle/nn/model.py:116-266),
+ * "<key> <float offset> <numel>\n". Returns the number of bytes needed (excluding the
+ * terminating NUL) or a negative AT_E_* code; writes at most `cap` bytes. */
+int64_t at_model_describe(const at_model_desc* desc, char* buf, int64_t cap);
+
 /* ---- engine ------------------------------------------------------------ */
 
 /* NeuralNetwork.__init__ (network.py:40-67): validates the configuration, sizes
