@@ -409,9 +409,11 @@ int launch_attention(const float* qkv, float* out, int64_t boards, int L, int d,
   const int dh = d / heads;
   const size_t smem = (size_t)2 * L * dh * sizeof(float);
   const unsigned grid = (unsigned)(boards * heads);
-#define AT_ATTN_CASE(DH)                                                                     \
-  case DH:                                                                                   \
-    attention_kernel<DH><<<grid, 128, smem, stream>>>(qkv, out, L, d, heads);                \
+#define AT_ATTN_CASE(DH)                                                                                             \
+  case DH:                                                                                                           \
+    if (smem > 48 * 1024)                                                                                            \
+      AT_CUDA_TRY(cudaFuncSetAttribute(attention_kernel<DH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)); \
+    attention_kernel<DH><<<grid, 128, smem, stream>>>(qkv, out, L, d, heads);                                        \
     break;
   switch (dh) {
     AT_ATTN_CASE(4)

@@ -63,7 +63,9 @@ def main():
     print("device:", torch.cuda.get_device_name(0))
     # ---- no swizzle ----
     a_img, b_img = image_interleaved(A), image_interleaved(B)
-    for hyp in ("lbo=K,sbo=MN", "lbo=MN,sbo=K"):
+    # (the swapped reading, lbo = M/N step and sbo = K step, was tried once on a B200: it walks outside the
+    #  image and faults with an illegal address, so it is not probed again)
+    for hyp in ("lbo=K,sbo=MN",):
         for shift in (0, 8, 16, 1, 17, 33):
             ref = A[shift : shift + 128] @ B.T
             if hyp == "lbo=K,sbo=MN":
