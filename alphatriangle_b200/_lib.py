@@ -18,6 +18,7 @@ FLAG_NONFINITE_OTHER = 2
 FLAG_NONFINITE_POLICY_LOGITS = 4
 FLAG_NONFINITE_VALUE_LOGITS = 8
 FLAG_NONFINITE_POLICY_PROBS = 16
+FLAG_PIPELINE_TIMEOUT = 0x80000000
 
 PREC_FP32, PREC_BF16 = 0, 1
 STATE_BYTES = 80
@@ -46,6 +47,8 @@ EXPORTS = (
     "at_engine_evaluate_packed",
     "at_engine_evaluate_host",
     "at_engine_last_launches",
+    "at_engine_kernel_ms",
+    "at_engine_bf16_trunk",
     "at_engine_action_dim",
     "at_probe_umma",
 )
@@ -116,6 +119,8 @@ def _bind(lib: C.CDLL) -> None:
         "at_engine_evaluate_packed": (i32, [vp, i32, vp, i64, vp, vp, vp, vp]),
         "at_engine_evaluate_host": (i32, [vp, i32, vp, i64, vp, vp, vp, vp]),
         "at_engine_last_launches": (i64, [vp]),
+        "at_engine_bf16_trunk": (i32, [vp, vp, i64, vp, vp]),
+        "at_engine_kernel_ms": (i32, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
         "at_engine_action_dim": (i32, [vp]),
         "at_probe_umma": (i32, [vp, i64, vp, i64, i32, i32, u32, u32, u32, u32, u32, u32, u32, u32, i32, vp, vp, vp]),
     }

@@ -1,19 +1,709 @@
-// tcgen05 / TMEM bf16 path -- placeholder until the tower kernels land.
+// tcgen05 / TMEM bf16 path (sm_100a): convolution tower + trunk FC as implicit GEMMs.
+//
+// tower_kernel  persistent, one CTA per SM, two boards in flight per CTA. A board's
+//               activations never leave shared memory between layers: they live as a
+//               zero-haloed 16-wide board image, [channel/8][162 rows][8 ch] bf16, so the
+//               nine taps of a 3x3 convolution are nine ROW-SHIFTED views of one image and
+//               each tap/channel-block is one tcgen05.mma (M=128 padded positions, N=Cout,
+//               K=16) whose A descriptor merely starts 16*(dy*16+dx) bytes further on.
+//               Weights (BatchNorm folded, bf16, pre-tiled as core matrices) stream from L2
+//               through a bulk-copy (TMA engine) ring and are shared by both boards;
+//               accumulators sit in TMEM (2 x 128 columns); eight epilogue warps apply
+//               bias / residual / activation and write the next layer's image.
+//               Layer 0 (Cin = 1, K = 9) is CUDA-core work in the prologue, straight from
+//               the PackedState bitmasks -- the occupancy grid is never materialised.
+// fc_kernel     trunk FC [B, H*W*C] x [H*W*C, N] as a split-K tcgen05 GEMM over the tower's
+//               output (written by the tower directly as A-operand tiles), fp32 partials.
+//
+// Reference semantics: alphatriangle/nn/model.py:15-60 (conv_block, ResidualBlock),
+// :232-240 (shared_fc), :268-297 (forward). Parity contract for this path: policy
+// KL <= 1e-3 against the fp32 reference (north_star).
+
+#include <cuda_bf16.h>
+
+#include <vector>
+
 #include "at_bf16.cuh"
+#include "at_fp32.cuh"
+#include "at_umma.cuh"
 
 namespace at {
 
-struct Bf16Path {};
+namespace {
 
-int bf16_create(const Plan&, int64_t, Bf16Path** out, std::string* reason) {
+using namespace umma;
+
+// ---- geometry of the on-chip board image --------------------------------------------
+constexpr int kPadW = 16;                    // board row stride: cols + at least one shared zero column
+constexpr int kM = 128;                      // MMA rows = padded positions y*16 + x
+constexpr int kHalo = 17;                    // zero rows before / after: max |dy*16 + dx|
+constexpr int kImgRows = kM + 2 * kHalo;     // 162
+constexpr int kPlaneBytes = kImgRows * 16;   // one 8-channel plane: 162 rows x 16 B
+constexpr int kMaxCh = 128;
+constexpr int kBufBytes = (kMaxCh / 8) * kPlaneBytes;  // 41,472
+constexpr int kStageBytes = 16384;
+constexpr int kStages = 3;
+constexpr int kMaxLayers = 12;
+constexpr int kMaxSlabs = 32;                // weight slabs per layer (9 taps x 128 channels / 64 = 18 at the defaults)
+constexpr int kBoards = 2;                   // boards in flight per CTA
+constexpr int kTowerThreads = 64 + kBoards * 128;
+constexpr long long kTimeoutCycles = 2000000000LL;  // ~1 s: a wedged pipeline reports instead of hanging
+
+struct TowerLayer {
+  int cin, cout, taps, ks, n_slabs;
+  int src, dst, res;  // buffer ids 0/1; dst = 2 -> global FC operand; res = -1 -> none
+  int act;
+  int bias_slot;
+  uint32_t slab_bytes;
+};
+
+struct TowerParams {
+  const PackedState* states;
+  int64_t batch;
+  const uint8_t* wstream;  // all MMA layers' weight slabs, in execution order
+  const float* bias;       // [n_layers][128] fp32
+  const float* w0;         // layer 0: [taps][c0] fp32 (folded), taps = 9
+  const float* b0;         // [c0]
+  int c0, act0;
+  int n_layers;
+  TowerLayer layers[kMaxLayers];
+  uint8_t* fc_a;           // output: [ceil(B/128)][n_kc][128][8] bf16
+  int n_kc;                // L * C_last / 8
+  int rows, cols;
+  uint32_t* status;
+};
+
+constexpr size_t tower_smem_bytes() {
+  return (size_t)kStages * kStageBytes + (size_t)kBoards * 2 * kBufBytes + (size_t)kMaxLayers * 128 * 4 + 9 * 128 * 4 + 128 * 4 +
+         (size_t)kMaxLayers * kMaxSlabs * 4 + (2 * kStages + 2) * 8 + 16;
+}
+
+__device__ __forceinline__ bool wait_bar(uint32_t bar, uint32_t parity, uint32_t* status, uint32_t code) {
+  const long long t0 = clock64();
+  while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > kTimeoutCycles) {
+      atomicOr(status, code);
+      return false;
+    }
+  }
+  return true;
+}
+
+__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
+__device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
+
+__global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_constant__ TowerParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint8_t* ring = smem;
+  uint8_t* act = ring + kStages * kStageBytes;                        // [board][buf][kBufBytes]
+  float* s_bias = reinterpret_cast<float*>(act + kBoards * 2 * kBufBytes);  // [kMaxLayers][128]
+  float* s_w0 = s_bias + kMaxLayers * 128;                            // [9][c0]
+  float* s_b0 = s_w0 + 9 * 128;                                       // [c0]
+  uint32_t* s_aoff = reinterpret_cast<uint32_t*>(s_b0 + 128);          // [kMaxLayers][kMaxSlabs]: A start of each slab's first MMA, >> 4
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_aoff + kMaxLayers * kMaxSlabs);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 2);
+
+  const int tid = threadIdx.x, warp = tid / 32, lane = tid % 32;
+  const uint32_t ring_u = smem_u32(ring), act_u = smem_u32(act);
+  const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + kStages);
+  const uint32_t bar_acc = smem_u32(bars + 2 * kStages), bar_act = smem_u32(bars + 2 * kStages + 1);
+
+  // ---- one-time setup --------------------------------------------------------------------
+  for (int i = tid; i < kBoards * 2 * kBufBytes / 16; i += kTowerThreads) reinterpret_cast<uint4*>(act)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = tid; i < p.n_layers * 128; i += kTowerThreads) s_bias[i] = p.bias[i];
+  for (int i = tid; i < 9 * p.c0; i += kTowerThreads) s_w0[i] = p.w0[i];
+  for (int i = tid; i < p.c0; i += kTowerThreads) s_b0[i] = p.b0[i];
+  // Where each weight slab's first MMA reads its A operand, relative to the layer's source image: the slab covers
+  // channels [c0, c0 + ks) of one tap, i.e. plane c0/8 of the image, shifted by (dy*16 + dx) rows.
+  for (int i = tid; i < p.n_layers * kMaxSlabs; i += kTowerThreads) {
+    const TowerLayer& L = p.layers[i / kMaxSlabs];
+    const int sl = i % kMaxSlabs;
+    uint32_t off = 0;
+    if (sl < L.n_slabs) {
+      const int k0 = sl * L.ks;
+      const int tap = k0 / L.cin, c0 = k0 - tap * L.cin;
+      const int shift = L.taps == 9 ? (tap / 3 - 1) * kPadW + (tap % 3 - 1) : 0;
+      off = (uint32_t)((c0 / 8) * kPlaneBytes + (kHalo + shift) * 16) >> 4;
+    }
+    s_aoff[i] = off;
+  }
+  if (tid == 0) {
+    for (int i = 0; i < kStages; ++i) {
+      mbar_init(bar_full + 8 * i, 1);
+      mbar_init(bar_empty + 8 * i, 1);
+    }
+    mbar_init(bar_acc, 1);
+    mbar_init(bar_act, kBoards * 4);  // one arrival per epilogue warp
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(smem_u32(tmem_slot), kBoards * 128);
+    tmem_relinquish();
+  }
+  fence_proxy_async_smem();  // the zeroed halos are read by the tensor core (async proxy)
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int64_t n_pairs = (p.batch + kBoards - 1) / kBoards;
+
+  if (warp == 0) {
+    // ===== weight producer: one lane streams every layer's slabs through the ring =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      bool ok = true;
+      for (int64_t pair = blockIdx.x; pair < n_pairs && ok; pair += gridDim.x) {
+        const uint8_t* src = p.wstream;
+        for (int l = 0; l < p.n_layers && ok; ++l) {
+          const uint32_t bytes = p.layers[l].slab_bytes;
+          for (int s = 0; s < p.layers[l].n_slabs; ++s) {
+            ok = wait_bar(bar_empty + 8 * stage, phase ^ 1, p.status, 1u);
+            if (!ok) break;
+            mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
+            bulk_g2s(ring_u + stage * kStageBytes, src, bytes, bar_full + 8 * stage);
+            src += bytes;
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer: a single thread drives the tensor core =====
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0, act_phase = 0;
+      bool ok = true;
+      for (int64_t pair = blockIdx.x; pair < n_pairs && ok; pair += gridDim.x) {
+        for (int l = 0; l < p.n_layers && ok; ++l) {
+          const TowerLayer& L = p.layers[l];
+          ok = wait_bar(bar_act, act_phase, p.status, 2u);  // this layer's input images are written
+          if (!ok) break;
+          act_phase ^= 1;
+          tc_fence_after();
+          const uint32_t idesc = idesc_bf16(kM, (uint32_t)L.cout);
+          const uint32_t b_lbo16 = (uint32_t)L.cout;  // bytes between 8-channel planes of a slab, >> 4
+          const int mma_per_slab = L.ks / 16;
+          const int n_slabs = L.n_slabs;
+          // descriptor halves that do not change inside the layer (see umma::smem_desc)
+          const uint32_t desc_hi = (128u >> 4) | (1u << 14);                       // SBO = 128 B, version 1, no swizzle
+          const uint32_t a_lo_fixed = (uint32_t)(kPlaneBytes >> 4) << 16;          // LBO = one 8-channel plane
+          const uint32_t b_lo_fixed = b_lbo16 << 16;
+          uint32_t a_img16[kBoards];
+#pragma unroll
+          for (int b = 0; b < kBoards; ++b) a_img16[b] = (act_u + (uint32_t)(b * 2 + L.src) * kBufBytes) >> 4;
+          const uint32_t* aoff = s_aoff + l * kMaxSlabs;
+          for (int s = 0; s < n_slabs; ++s) {
+            const uint32_t a_off16 = aoff[s];
+            ok = wait_bar(bar_full + 8 * stage, phase, p.status, 4u);
+            if (!ok) break;
+            tc_fence_after();
+            const uint32_t b16 = (ring_u + stage * kStageBytes) >> 4;
+#pragma unroll
+            for (int b = 0; b < kBoards; ++b) {
+#pragma unroll 4
+              for (int j = 0; j < mma_per_slab; ++j) {
+                const uint32_t a_lo = a_lo_fixed | (a_img16[b] + a_off16 + (uint32_t)j * (2 * kPlaneBytes >> 4));
+                const uint32_t b_lo = b_lo_fixed | (b16 + (uint32_t)j * 2 * b_lbo16);
+                mma_bf16(tmem_base + (uint32_t)b * 128, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo, idesc,
+                         (s | j) != 0);
+              }
+            }
+            mma_commit(bar_empty + 8 * stage);  // slab may be overwritten once these MMAs retire
+            if (++stage == kStages) { stage = 0; phase ^= 1; }
+          }
+          if (ok) mma_commit(bar_acc);  // both boards' accumulators are complete
+        }
+      }
+    }
+  } else {
+    // ===== epilogue warps: 4 per board; warp%4 selects the TMEM lane quarter =====
+    const int eb = (warp - 2) / 4;
+    const int q = warp % 4;
+    const int m = q * 32 + lane;  // padded position = MMA row = TMEM lane
+    const int y = m / kPadW, x = m % kPadW;
+    const bool inside = (y < p.rows) && (x < p.cols);
+    const int pos = y * p.cols + x;  // compact position index (token order h*W + w)
+    uint8_t* my_act = act + (size_t)eb * 2 * kBufBytes;
+    uint32_t acc_phase = 0;
+    bool ok = true;
+    for (int64_t pair = blockIdx.x; pair < n_pairs && ok; pair += gridDim.x) {
+      const int64_t board = pair * kBoards + eb;
+      const bool valid = board < p.batch;
+      // ---- layer 0 on CUDA cores, straight from the bitmasks (extractor.py:33-46 + conv_body.0) ----
+      {
+        float g[9];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) g[t] = 0.0f;
+        if (valid) {
+          const PackedState& st = p.states[board];
+#pragma unroll
+          for (int t = 0; t < 9; ++t) {
+            const int yy = y + t / 3 - 1, xx = x + t % 3 - 1;
+            if (yy >= 0 && yy < p.rows && xx >= 0 && xx < p.cols) {
+              const int i = yy * p.cols + xx;
+              const uint32_t bit = 1u << (i & 31);
+              g[t] = (st.death[i >> 5] & bit) ? -1.0f : ((st.occ[i >> 5] & bit) ? 1.0f : 0.0f);
+            }
+          }
+        }
+        uint8_t* dst = my_act + 0 * kBufBytes + (size_t)(kHalo + m) * 16;
+        for (int c8 = 0; c8 < p.c0; c8 += 8) {
+          float v[8];
+#pragma unroll
+          for (int j = 0; j < 8; ++j) {
+            float a = s_b0[c8 + j];
+#pragma unroll
+            for (int t = 0; t < 9; ++t) a = fmaf(g[t], s_w0[t * p.c0 + c8 + j], a);
+            v[j] = inside ? apply_act(a, p.act0) : 0.0f;
+          }
+          *reinterpret_cast<uint4*>(dst + (size_t)(c8 / 8) * kPlaneBytes) =
+              make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+        }
+      }
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_act);
+
+      for (int l = 0; l < p.n_layers; ++l) {
+        const TowerLayer& L = p.layers[l];
+        ok = wait_bar(bar_acc, acc_phase, p.status, 8u);
+        if (!ok) break;
+        acc_phase ^= 1;
+        tc_fence_after();
+        const float* bias = s_bias + L.bias_slot * 128;
+        const uint8_t* res = L.res >= 0 ? my_act + (size_t)L.res * kBufBytes + (size_t)(kHalo + m) * 16 : nullptr;
+        for (int c0 = 0; c0 < L.cout; c0 += 32) {
+          uint32_t r[32];
+          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(eb * 128 + c0), r);
+          tmem_ld_wait();
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            float v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[i * 8 + j]) + bias[c0 + i * 8 + j];
+            if (res) {
+              const uint4 rv = *reinterpret_cast<const uint4*>(res + (size_t)((c0 + i * 8) / 8) * kPlaneBytes);
+              v[0] += bf16_lo(rv.x); v[1] += bf16_hi(rv.x); v[2] += bf16_lo(rv.y); v[3] += bf16_hi(rv.y);
+              v[4] += bf16_lo(rv.z); v[5] += bf16_hi(rv.z); v[6] += bf16_lo(rv.w); v[7] += bf16_hi(rv.w);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = inside ? apply_act(v[j], L.act) : 0.0f;
+            const uint4 out = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+            const int chunk = (c0 + i * 8) / 8;
+            if (L.dst < 2) {
+              *reinterpret_cast<uint4*>(my_act + (size_t)L.dst * kBufBytes + (size_t)chunk * kPlaneBytes + (size_t)(kHalo + m) * 16) = out;
+            } else if (valid && inside) {
+              const int64_t kc = (int64_t)pos * (L.cout / 8) + chunk;
+              uint8_t* gdst = p.fc_a + (((board >> 7) * p.n_kc + kc) * 128 + (board & 127)) * 16;
+              *reinterpret_cast<uint4*>(gdst) = out;
+            }
+          }
+        }
+        tc_fence_before();  // TMEM reads are done before the next layer's MMAs overwrite the accumulator
+        if (l + 1 < p.n_layers) {
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar_act);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, kBoards * 128);
+}
+
+// ---- trunk FC: split-K tcgen05 GEMM ---------------------------------------------------------
+constexpr int kFcStages = 4;
+constexpr int kFcThreads = 192;
+
+struct FcParams {
+  const uint8_t* a;  // [Mtiles][n_kc][128][8] bf16
+  const uint8_t* w;  // [n_kc][N][8] bf16
+  float* partial;    // [splits][batch][N]
+  int64_t batch;
+  int n_kc, N, slabs_per_split, n_slabs;
+  uint32_t* status;
+};
+
+constexpr size_t fc_smem_bytes() { return (size_t)kFcStages * 2 * kStageBytes + (2 * kFcStages + 1) * 8 + 16; }
+
+__global__ void __launch_bounds__(kFcThreads, 1) fc_kernel(const __grid_constant__ FcParams p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kFcStages * 2 * kStageBytes);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kFcStages + 1);
+  const int tid = threadIdx.x, warp = tid / 32, lane = tid % 32;
+  const uint32_t smem_u = smem_u32(smem);
+  const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + kFcStages), bar_acc = smem_u32(bars + 2 * kFcStages);
+  uint32_t cols = 32;
+  while (cols < (uint32_t)p.N) cols <<= 1;
+
+  if (tid == 0) {
+    for (int i = 0; i < kFcStages; ++i) {
+      mbar_init(bar_full + 8 * i, 1);
+      mbar_init(bar_empty + 8 * i, 1);
+    }
+    mbar_init(bar_acc, 1);
+    fence_mbar_init();
+  }
+  if (warp == 0) {
+    tmem_alloc(smem_u32(tmem_slot), cols);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int mt = blockIdx.x, z = blockIdx.y;
+  const int s_begin = z * p.slabs_per_split;
+  const int s_end = min(p.n_slabs, s_begin + p.slabs_per_split);
+  const uint32_t b_bytes = (uint32_t)p.N * 128;  // 8 chunks x N rows x 16 B
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int s = s_begin; s < s_end; ++s) {
+        if (!wait_bar(bar_empty + 8 * stage, phase ^ 1, p.status, 16u)) break;
+        mbar_arrive_expect_tx(bar_full + 8 * stage, kStageBytes + b_bytes);
+        bulk_g2s(smem_u + stage * 2 * kStageBytes, p.a + ((size_t)mt * p.n_kc + (size_t)s * 8) * 2048, kStageBytes, bar_full + 8 * stage);
+        bulk_g2s(smem_u + stage * 2 * kStageBytes + kStageBytes, p.w + (size_t)s * b_bytes, b_bytes, bar_full + 8 * stage);
+        if (++stage == kFcStages) { stage = 0; phase ^= 1; }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      const uint32_t idesc = idesc_bf16(kM, (uint32_t)p.N);
+      const uint32_t b_lbo = (uint32_t)p.N * 16;
+      bool ok = true;
+      for (int s = s_begin; s < s_end; ++s) {
+        ok = wait_bar(bar_full + 8 * stage, phase, p.status, 32u);
+        if (!ok) break;
+        tc_fence_after();
+        const uint32_t a_base = smem_u + stage * 2 * kStageBytes, b_base = a_base + kStageBytes;
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint64_t da = smem_desc(a_base + (uint32_t)(2 * j) * 2048, 2048, 128, LAYOUT_NONE);
+          const uint64_t db = smem_desc(b_base + (uint32_t)(2 * j) * b_lbo, b_lbo, 128, LAYOUT_NONE);
+          mma_bf16(tmem_base, da, db, idesc, (s != s_begin) || j != 0);
+        }
+        mma_commit(bar_empty + 8 * stage);
+        if (++stage == kFcStages) { stage = 0; phase ^= 1; }
+      }
+      mma_commit(bar_acc);
+    }
+  } else {
+    const int q = warp % 4;
+    const int m = q * 32 + lane;
+    const int64_t board = (int64_t)mt * 128 + m;
+    if (wait_bar(bar_acc, 0, p.status, 64u)) {
+      tc_fence_after();
+      float* dst = p.partial + ((int64_t)z * p.batch + board) * p.N;
+      for (int c0 = 0; c0 < p.N; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, r);
+        tmem_ld_wait();
+        if (board < p.batch && s_end > s_begin) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (c0 + i * 4 < p.N)
+              *reinterpret_cast<float4*>(dst + c0 + i * 4) = make_float4(__uint_as_float(r[i * 4]), __uint_as_float(r[i * 4 + 1]),
+                                                                         __uint_as_float(r[i * 4 + 2]), __uint_as_float(r[i * 4 + 3]));
+        } else if (board < p.batch) {
+#pragma unroll
+          for (int i = 0; i < 8; ++i)
+            if (c0 + i * 4 < p.N) *reinterpret_cast<float4*>(dst + c0 + i * 4) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, cols);
+}
+
+// fp32 [K,N] (row k contiguous in n) -> bf16 core-matrix tiles [K/8][N][8]
+__global__ void __launch_bounds__(256) pack_b_kernel(const float* __restrict__ wt, int K, int N, __nv_bfloat16* __restrict__ dst) {
+  const int64_t total = (int64_t)K * N;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t kc = i / ((int64_t)N * 8);
+    const int rem = (int)(i - kc * N * 8);
+    const int n = rem / 8, e = rem % 8;
+    dst[i] = __float2bfloat16_rn(wt[(kc * 8 + e) * N + n]);
+  }
+}
+
+__global__ void gather_bias_kernel(const float* __restrict__ folded, const int64_t* __restrict__ offs, const int* __restrict__ widths,
+                                   int n_layers, float* __restrict__ dst) {
+  const int l = blockIdx.x;
+  if (l >= n_layers) return;
+  for (int i = threadIdx.x; i < 128; i += blockDim.x) dst[l * 128 + i] = i < widths[l] ? folded[offs[l] + i] : 0.0f;
+}
+
+}  // namespace
+
+// ---- host side ---------------------------------------------------------------------------------
+
+struct Bf16Path {
+  TowerParams tp{};           // template: pointers filled per call
+  std::vector<int64_t> layer_wt;  // folded-set offset of each MMA layer's Wt
+  std::vector<int> layer_k;
+  std::vector<int64_t> bias_off;
+  std::vector<int> bias_w;
+  int64_t w0_off = 0, b0_off = 0;
+  size_t wstream_bytes = 0;
+  // per weight set
+  uint8_t* wstream[2] = {nullptr, nullptr};
+  uint8_t* wfc[2] = {nullptr, nullptr};
+  float* bias[2] = {nullptr, nullptr};
+  int64_t* d_bias_off = nullptr;
+  int* d_bias_w = nullptr;
+  // trunk FC
+  int fc_n = 0, fc_flat = 0, n_kc = 0;
+  int64_t fc_wt = 0;
+  // scratch
+  int64_t max_batch = 0;
+  uint8_t* fc_a = nullptr;
+  float* partial = nullptr;
+  int max_splits = 0;
+  float* other = nullptr;
+  float* grid = nullptr;
+  uint32_t* status = nullptr;
+  int sms = 148;
+  cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // tower begin/end, fc begin/end
+  bool timed = false;
+};
+
+int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* reason) {
   *out = nullptr;
-  *reason = "tcgen05 tower not built yet";
+  const at_model_desc& d = p.d;
+  auto no = [&](const std::string& why) {
+    *reason = why;
+    return AT_OK;
+  };
+  if (p.transformer) return no("transformer layers are not on the tcgen05 path yet");
+  if (d.grid_channels != 1) return no("GRID_INPUT_CHANNELS must be 1");
+  if (d.env.rows * kPadW > kM || d.env.cols + 1 > kPadW) return no("board must fit a 16-wide, 128-position padded image (ROWS <= 8, COLS <= 15)");
+  if (p.convs.empty()) return no("needs at least one conv_body layer");
+  if (p.shared.empty()) return no("needs at least one shared FC layer");
+  std::vector<const ConvLayer*> seq;
+  for (const ConvLayer& c : p.convs) seq.push_back(&c);
+  if (p.has_res_proj) seq.push_back(&p.res_proj);
+  for (const ResBlock& r : p.res) {
+    seq.push_back(&r.c1);
+    seq.push_back(&r.c2);
+  }
+  if ((int)seq.size() - 1 > kMaxLayers || seq.size() < 2) return no("needs 2..13 convolution layers");
+  for (size_t i = 0; i < seq.size(); ++i) {
+    const ConvLayer& c = *seq[i];
+    const bool k3 = c.kh == 3 && c.kw == 3 && c.ph == 1 && c.pw == 1;
+    const bool k1 = c.kh == 1 && c.kw == 1 && c.ph == 0 && c.pw == 0;
+    if (c.sh != 1 || c.sw != 1 || !(k3 || (k1 && i > 0))) return no("convolutions must be 3x3 stride 1 pad 1 (or the 1x1 projection)");
+    if (c.cout % 16 != 0 || c.cout > kMaxCh || (i > 0 && c.cin % 16 != 0)) return no("channel counts must be multiples of 16, at most 128");
+    if (c.cout % 32 != 0) return no("channel counts must be multiples of 32");
+  }
+  const Affine& fc = p.shared[0];
+  if (fc.N % 32 != 0 || fc.N > 128) return no("first shared FC width must be a multiple of 32, at most 128");
+  if ((p.flat % 64) != 0) return no("flattened trunk size must be a multiple of 64");
+
+  Bf16Path* b = new Bf16Path();
+  TowerParams& tp = b->tp;
+  tp.rows = d.env.rows;
+  tp.cols = d.env.cols;
+  tp.c0 = seq[0]->cout;
+  tp.act0 = seq[0]->f.act;
+  b->w0_off = seq[0]->f.wt;
+  b->b0_off = seq[0]->f.bias;
+  tp.n_layers = (int)seq.size() - 1;
+  // buffer choreography: layer 0 writes buffer 0; plain layers ping-pong; a residual block's second conv
+  // adds the block input (still sitting in the other buffer) and overwrites it in place.
+  int cur = 0;
+  size_t li = 1;
+  int slot = 0;
+  auto add = [&](const ConvLayer& c, int src, int dst, int res) {
+    TowerLayer& L = tp.layers[slot];
+    L.cin = c.cin; L.cout = c.cout; L.taps = c.kh * c.kw;
+    L.ks = c.cin >= 64 ? 64 : c.cin;
+    while ((L.taps * c.cin) % L.ks) L.ks /= 2;
+    L.n_slabs = L.taps * c.cin / L.ks;
+    L.slab_bytes = (uint32_t)L.ks * c.cout * 2;
+    L.src = src; L.dst = dst; L.res = res; L.act = c.f.act; L.bias_slot = slot;
+    b->layer_wt.push_back(c.f.wt);
+    b->layer_k.push_back(c.f.K);
+    b->bias_off.push_back(c.f.bias);
+    b->bias_w.push_back(c.cout);
+    b->wstream_bytes += (size_t)c.f.K * c.cout * 2;
+    ++slot;
+  };
+  const size_t n_plain = p.convs.size() + (p.has_res_proj ? 1 : 0);
+  for (; li < n_plain; ++li) {
+    add(*seq[li], cur, cur ^ 1, -1);
+    cur ^= 1;
+  }
+  for (size_t r = 0; r < p.res.size(); ++r) {
+    add(p.res[r].c1, cur, cur ^ 1, -1);
+    add(p.res[r].c2, cur ^ 1, cur, cur);
+  }
+  if (n_plain == 1 && p.res.empty()) {
+    delete b;
+    return no("needs a tensor-core layer after the first convolution");
+  }
+  tp.layers[tp.n_layers - 1].dst = 2;
+  const int c_last = tp.layers[tp.n_layers - 1].cout;
+  b->n_kc = p.L * c_last / 8;
+  tp.n_kc = b->n_kc;
+  b->fc_n = fc.N;
+  b->fc_flat = p.flat;
+  b->fc_wt = fc.wt;
+  b->max_batch = max_batch;
+
+  cudaDeviceProp prop;
+  int dev = 0;
+  cudaGetDevice(&dev);
+  cudaGetDeviceProperties(&prop, dev);
+  b->sms = prop.multiProcessorCount;
+  const int64_t m_tiles = (max_batch + 127) / 128;
+  b->max_splits = 16;
+  auto alloc = [&]() -> int {
+    for (int i = 0; i < 2; ++i) {
+      AT_CUDA_TRY(cudaMalloc(&b->wstream[i], b->wstream_bytes));
+      AT_CUDA_TRY(cudaMalloc(&b->wfc[i], (size_t)p.flat * fc.N * 2));
+      AT_CUDA_TRY(cudaMalloc(&b->bias[i], (size_t)kMaxLayers * 128 * sizeof(float)));
+    }
+    AT_CUDA_TRY(cudaMalloc(&b->d_bias_off, kMaxLayers * sizeof(int64_t)));
+    AT_CUDA_TRY(cudaMalloc(&b->d_bias_w, kMaxLayers * sizeof(int)));
+    AT_CUDA_TRY(cudaMemcpy(b->d_bias_off, b->bias_off.data(), b->bias_off.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
+    AT_CUDA_TRY(cudaMemcpy(b->d_bias_w, b->bias_w.data(), b->bias_w.size() * sizeof(int), cudaMemcpyHostToDevice));
+    AT_CUDA_TRY(cudaMalloc(&b->fc_a, (size_t)m_tiles * b->n_kc * 2048));
+    AT_CUDA_TRY(cudaMemset(b->fc_a, 0, (size_t)m_tiles * b->n_kc * 2048));
+    AT_CUDA_TRY(cudaMalloc(&b->partial, (size_t)(b->max_splits + 1) * max_batch * fc.N * sizeof(float)));
+    AT_CUDA_TRY(cudaMalloc(&b->other, (size_t)max_batch * d.other_dim * sizeof(float)));
+    AT_CUDA_TRY(cudaMalloc(&b->grid, (size_t)max_batch * d.env.rows * d.env.cols * sizeof(float)));
+    AT_CUDA_TRY(cudaMalloc(&b->status, 4 * sizeof(uint32_t)));
+    AT_CUDA_TRY(cudaMemset(b->status, 0, 4 * sizeof(uint32_t)));
+    for (auto& e : b->ev) AT_CUDA_TRY(cudaEventCreate(&e));
+    AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+    AT_CUDA_TRY(cudaFuncSetAttribute(fc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fc_smem_bytes()));
+    return AT_OK;
+  };
+  const int rc = alloc();
+  if (rc != AT_OK) {
+    bf16_destroy(b);
+    return rc;
+  }
+  *out = b;
   return AT_OK;
 }
-void bf16_destroy(Bf16Path* p) { delete p; }
-int bf16_pack_weights(Bf16Path*, const Plan&, const float*, int, cudaStream_t) { return AT_OK; }
-int bf16_evaluate(Bf16Path*, const Plan&, const float*, int, const void*, int64_t, float*, float*, uint32_t*, cudaStream_t, int64_t*) {
-  return fail(AT_E_UNSUPPORTED, "bf16 path not built");
+
+void bf16_destroy(Bf16Path* b) {
+  if (!b) return;
+  for (int i = 0; i < 2; ++i) {
+    cudaFree(b->wstream[i]);
+    cudaFree(b->wfc[i]);
+    cudaFree(b->bias[i]);
+  }
+  cudaFree(b->d_bias_off);
+  cudaFree(b->d_bias_w);
+  cudaFree(b->fc_a);
+  cudaFree(b->partial);
+  cudaFree(b->other);
+  cudaFree(b->grid);
+  cudaFree(b->status);
+  for (auto& e : b->ev)
+    if (e) cudaEventDestroy(e);
+  delete b;
+}
+
+int bf16_pack_weights(Bf16Path* b, const Plan& p, const float* folded, int slot, cudaStream_t st) {
+  size_t off = 0;
+  for (size_t l = 0; l < b->layer_wt.size(); ++l) {
+    const int K = b->layer_k[l], N = b->bias_w[l];
+    pack_b_kernel<<<148, 256, 0, st>>>(folded + b->layer_wt[l], K, N, reinterpret_cast<__nv_bfloat16*>(b->wstream[slot] + off));
+    AT_CUDA_TRY(cudaGetLastError());
+    off += (size_t)K * N * 2;
+  }
+  pack_b_kernel<<<148 * 4, 256, 0, st>>>(folded + b->fc_wt, b->fc_flat, b->fc_n, reinterpret_cast<__nv_bfloat16*>(b->wfc[slot]));
+  AT_CUDA_TRY(cudaGetLastError());
+  gather_bias_kernel<<<(unsigned)b->layer_wt.size(), 128, 0, st>>>(folded, b->d_bias_off, b->d_bias_w, (int)b->layer_wt.size(), b->bias[slot]);
+  AT_CUDA_TRY(cudaGetLastError());
+  (void)p;
+  return AT_OK;
+}
+
+int bf16_trunk(Bf16Path* b, const Plan& p, const float* folded, int slot, const void* d_states, int64_t batch, float* d_trunk,
+               cudaStream_t st, int64_t* launches) {
+  const at_model_desc& d = p.d;
+  // "other" features for the FC's last columns (the grid output of this launch is not used by the tower)
+  AT_TRY(launch_features(d.env, 1, d.other_dim, d_states, batch, b->grid, b->other, st));
+  ++*launches;
+
+  TowerParams tp = b->tp;
+  tp.states = static_cast<const PackedState*>(d_states);
+  tp.batch = batch;
+  tp.wstream = b->wstream[slot];
+  tp.bias = b->bias[slot];
+  tp.w0 = folded + b->w0_off;
+  tp.b0 = folded + b->b0_off;
+  tp.fc_a = b->fc_a;
+  tp.status = b->status;
+  const int64_t n_pairs = (batch + kBoards - 1) / kBoards;
+  const unsigned grid = (unsigned)(n_pairs < b->sms ? n_pairs : b->sms);
+  AT_CUDA_TRY(cudaEventRecord(b->ev[0], st));
+  tower_kernel<<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp);
+  AT_CUDA_TRY(cudaGetLastError());
+  AT_CUDA_TRY(cudaEventRecord(b->ev[1], st));
+  ++*launches;
+
+  // trunk FC: split-K so that M-tiles x splits covers the SMs about twice
+  const int m_tiles = (int)((batch + 127) / 128);
+  const int n_slabs = b->n_kc / 8;
+  int splits = (2 * b->sms + m_tiles - 1) / m_tiles;
+  if (splits > b->max_splits) splits = b->max_splits;
+  if (splits > n_slabs) splits = n_slabs;
+  if (splits < 1) splits = 1;
+  const int per = (n_slabs + splits - 1) / splits;
+  splits = (n_slabs + per - 1) / per;
+  FcParams fp{b->fc_a, b->wfc[slot], b->partial, batch, b->n_kc, b->fc_n, per, n_slabs, b->status};
+  AT_CUDA_TRY(cudaEventRecord(b->ev[2], st));
+  fc_kernel<<<dim3((unsigned)m_tiles, (unsigned)splits), kFcThreads, fc_smem_bytes(), st>>>(fp);
+  AT_CUDA_TRY(cudaGetLastError());
+  AT_CUDA_TRY(cudaEventRecord(b->ev[3], st));
+  ++*launches;
+  b->timed = true;
+
+  // the FC's "other" columns in fp32 as one more partial, then bias + BatchNorm (folded) + activation
+  const Affine& fc = p.shared[0];
+  GemmArgs o;
+  o.A = b->other; o.lda = d.other_dim; o.M = batch; o.N = fc.N; o.K = d.other_dim;
+  o.Wt = folded + fc.wt + (int64_t)p.flat * fc.N;
+  o.C = b->partial + (int64_t)splits * batch * fc.N; o.ldc = fc.N;
+  AT_TRY(launch_gemm(o, 1, st, launches));
+  GemmArgs f;
+  f.M = batch; f.N = fc.N; f.K = 1;
+  f.partial = b->partial; f.bias = folded + fc.bias; f.act = fc.act;
+  f.C = d_trunk; f.ldc = fc.N;
+  AT_TRY(launch_splitk_finish(f, splits + 1, st, launches));
+  return AT_OK;
+}
+
+const uint32_t* bf16_status_ptr(const Bf16Path* b) { return b->status; }
+
+int bf16_kernel_ms(Bf16Path* b, float* tower_ms, float* fc_ms) {
+  if (!b || !b->timed) return fail(AT_E_STATE, "no bf16 evaluation has run yet");
+  AT_CUDA_TRY(cudaEventSynchronize(b->ev[3]));
+  AT_CUDA_TRY(cudaEventElapsedTime(tower_ms, b->ev[0], b->ev[1]));
+  AT_CUDA_TRY(cudaEventElapsedTime(fc_ms, b->ev[2], b->ev[3]));
+  return AT_OK;
 }
 
 }  // namespace at

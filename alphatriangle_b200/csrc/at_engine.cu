@@ -115,6 +115,40 @@ int run_conv(at_engine* e, const ConvLayer& c, const float* W, const float* in, 
   return launch_gemm(g, 1, st, &e->last_launches);
 }
 
+// shared_fc[first_shared:] -> policy / value heads -> softmax + expected value (model.py:294-297, network.py:269-278)
+int run_heads(at_engine* e, const float* W, const float* x, int64_t ld, bool zero_padded, size_t first_shared, int64_t n, float* probs,
+              float* value, uint32_t* flags, cudaStream_t st) {
+  const Plan& p = e->plan;
+  const at_model_desc& d = p.d;
+  const float* trunk = x;
+  int64_t trunk_ld = ld;
+  {
+    float* pingpong[2] = {e->mlp_a, e->mlp_b};
+    int w2 = 0;
+    for (size_t i = first_shared; i < p.shared.size(); ++i) {
+      float* out = (i + 1 == p.shared.size()) ? e->trunk : pingpong[w2];
+      AT_TRY(run_affine(e, p.shared[i], W, trunk, trunk_ld, n, out, p.shared[i].N, nullptr, 0, st, zero_padded && i == 0));
+      trunk = out; trunk_ld = p.shared[i].N; w2 ^= 1;
+    }
+  }
+  auto head = [&](const std::vector<Affine>& layers, float* logits) -> int {
+    const float* hx = trunk;
+    int64_t hld = trunk_ld;
+    float* pingpong[2] = {e->mlp_a, e->mlp_b};
+    int w2 = 0;
+    for (size_t i = 0; i < layers.size(); ++i) {
+      float* out = (i + 1 == layers.size()) ? logits : pingpong[w2];
+      AT_TRY(run_affine(e, layers[i], W, hx, hld, n, out, layers[i].N, nullptr, 0, st));
+      hx = out; hld = layers[i].N; w2 ^= 1;
+    }
+    return AT_OK;
+  };
+  AT_TRY(head(p.policy, e->pol_logits));
+  AT_TRY(head(p.value, e->val_logits));
+  return launch_heads(e->pol_logits, e->val_logits, n, p.action_dim, d.num_atoms, d.v_min, d.v_max, probs, value, flags, st,
+                      &e->last_launches);
+}
+
 // AlphaTriangleNet.forward for `n` boards (n <= chunk) on the fp32 path.
 int forward_fp32_chunk(at_engine* e, const float* W, const float* grid, const float* other, int64_t n, float* probs, float* value,
                        uint32_t* flags, cudaStream_t st) {
@@ -199,34 +233,7 @@ int forward_fp32_chunk(at_engine* e, const float* W, const float* grid, const fl
 
   // ---- cat(other) -> shared_fc -> heads (model.py:292-297) ---------------------------------
   AT_TRY(launch_copy_rows(other, n, d.other_dim, e->concat + p.flat, p.concat_ld, st, &e->last_launches));
-  const float* trunk = e->concat;
-  int64_t trunk_ld = p.concat_ld;
-  {
-    float* pingpong[2] = {e->mlp_a, e->mlp_b};
-    int w2 = 0;
-    for (size_t i = 0; i < p.shared.size(); ++i) {
-      float* out = (i + 1 == p.shared.size()) ? e->trunk : pingpong[w2];
-      AT_TRY(run_affine(e, p.shared[i], W, trunk, trunk_ld, n, out, p.shared[i].N, nullptr, 0, st, /*a_zero_padded=*/i == 0));
-      trunk = out; trunk_ld = p.shared[i].N; w2 ^= 1;
-    }
-  }
-  auto head = [&](const std::vector<Affine>& layers, float* logits) -> int {
-    const float* x = trunk;
-    int64_t ld = trunk_ld;
-    float* pingpong[2] = {e->mlp_a, e->mlp_b};
-    int w2 = 0;
-    for (size_t i = 0; i < layers.size(); ++i) {
-      float* out = (i + 1 == layers.size()) ? logits : pingpong[w2];
-      AT_TRY(run_affine(e, layers[i], W, x, ld, n, out, layers[i].N, nullptr, 0, st));
-      x = out; ld = layers[i].N; w2 ^= 1;
-    }
-    return AT_OK;
-  };
-  AT_TRY(head(p.policy, e->pol_logits));
-  AT_TRY(head(p.value, e->val_logits));
-  AT_TRY(launch_heads(e->pol_logits, e->val_logits, n, p.action_dim, d.num_atoms, d.v_min, d.v_max, probs, value, flags, st,
-                      &e->last_launches));
-  return AT_OK;
+  return run_heads(e, W, e->concat, p.concat_ld, /*zero_padded=*/true, 0, n, probs, value, flags, st);
 }
 
 int begin_eval(at_engine* e, cudaStream_t st, const float** W) {
@@ -314,11 +321,12 @@ int at_engine_create(const at_model_desc* desc, int device, int64_t max_batch, a
     AT_TRY(dev_alloc(&e->concat, S * p.concat_ld));
     AT_CUDA_TRY(cudaMemset(e->concat, 0, (size_t)S * p.concat_ld * sizeof(float)));  // pad columns stay zero forever
     const int64_t mlp_w = p.max_mlp > 0 ? p.max_mlp : 1;
-    AT_TRY(dev_alloc(&e->mlp_a, S * mlp_w));
-    AT_TRY(dev_alloc(&e->mlp_b, S * mlp_w));
-    AT_TRY(dev_alloc(&e->trunk, S * mlp_w));
-    AT_TRY(dev_alloc(&e->pol_logits, S * p.action_dim));
-    AT_TRY(dev_alloc(&e->val_logits, S * (int64_t)p.d.num_atoms));
+    const int64_t H = max_batch;  // the heads run on whole batches (the bf16 trunk is not sliced)
+    AT_TRY(dev_alloc(&e->mlp_a, H * mlp_w));
+    AT_TRY(dev_alloc(&e->mlp_b, H * mlp_w));
+    AT_TRY(dev_alloc(&e->trunk, H * mlp_w));
+    AT_TRY(dev_alloc(&e->pol_logits, H * p.action_dim));
+    AT_TRY(dev_alloc(&e->val_logits, H * (int64_t)p.d.num_atoms));
     e->partial_floats = (int64_t)8192 * (p.max_n > 0 ? p.max_n : 1);
     AT_TRY(dev_alloc(&e->partial, e->partial_floats));
     AT_TRY(dev_alloc(&e->feat_grid, S * (int64_t)p.d.grid_channels * p.d.env.rows * p.d.env.cols));
@@ -403,6 +411,25 @@ int at_engine_supports(const at_engine* e, int precision) {
 int at_engine_action_dim(const at_engine* e) { return e ? e->plan.action_dim : 0; }
 int64_t at_engine_last_launches(const at_engine* e) { return e ? e->last_launches : 0; }
 
+int at_engine_kernel_ms(const at_engine* e, float* tower_ms, float* fc_ms) {
+  if (!e || !tower_ms || !fc_ms) return fail(AT_E_INVALID, "at_engine_kernel_ms: null argument");
+  if (!e->bf16) return fail(AT_E_UNSUPPORTED, "at_engine_kernel_ms: the bf16 path is not available");
+  DeviceGuard guard(e->device);
+  return bf16_kernel_ms(e->bf16, tower_ms, fc_ms);
+}
+
+int at_engine_bf16_trunk(at_engine* e, const void* d_states, int64_t batch, float* d_trunk, void* stream) {
+  if (!e || !d_states || !d_trunk) return fail(AT_E_INVALID, "at_engine_bf16_trunk: null argument");
+  if (batch <= 0 || batch > e->max_batch) return fail(AT_E_INVALID, "at_engine_bf16_trunk: batch out of range");
+  AT_TRY(check_precision(e, AT_PREC_BF16));
+  DeviceGuard guard(e->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const float* W = nullptr;
+  AT_TRY(begin_eval(e, st, &W));
+  AT_TRY(bf16_trunk(e->bf16, e->plan, W, e->active, d_states, batch, d_trunk, st, &e->last_launches));
+  return end_eval(e, st);
+}
+
 int at_engine_forward(at_engine* e, int precision, const float* d_grid, const float* d_other, int64_t batch, float* d_policy,
                       float* d_value, uint32_t* d_flags, void* stream) {
   if (!e) return fail(AT_E_INVALID, "at_engine_forward: null engine");
@@ -443,7 +470,10 @@ int at_engine_evaluate_packed(at_engine* e, int precision, const void* d_states,
   const Plan& p = e->plan;
   if (precision == AT_PREC_BF16) {
     if (batch > e->max_batch) return fail(AT_E_INVALID, "at_engine_evaluate_packed: batch exceeds the engine's max_batch");
-    AT_TRY(bf16_evaluate(e->bf16, p, W, e->active, d_states, batch, d_policy, d_value, d_flags, st, &e->last_launches));
+    float* trunk1 = p.shared.size() == 1 ? e->trunk : e->mlp_b;
+    AT_TRY(bf16_trunk(e->bf16, p, W, e->active, d_states, batch, trunk1, st, &e->last_launches));
+    AT_TRY(run_heads(e, W, trunk1, p.shared[0].N, false, 1, batch, d_policy, d_value, d_flags, st));
+    AT_TRY(launch_merge_status(bf16_status_ptr(e->bf16), d_flags, st, &e->last_launches));
     return end_eval(e, st);
   }
   const char* states = static_cast<const char*>(d_states);

@@ -342,6 +342,11 @@ __global__ void __launch_bounds__(256) copy_rows_kernel(const float* __restrict_
   }
 }
 
+// pipeline-timeout bits of the tcgen05 kernels -> bit 31 (+ detail in bits 8..15) of the caller's flag word
+__global__ void merge_status_kernel(const uint32_t* __restrict__ status, uint32_t* __restrict__ flags) {
+  if (threadIdx.x == 0 && *status) atomicOr(flags, 0x80000000u | ((*status & 0xFFu) << 8));
+}
+
 inline unsigned grid_for(int64_t total, int threads, int cap = 148 * 16) {
   int64_t blocks = (total + threads - 1) / threads;
   if (blocks < 1) blocks = 1;
@@ -386,6 +391,27 @@ int launch_gemm(const GemmArgs& g_in, int splits, cudaStream_t stream, int64_t* 
     AT_CUDA_TRY(cudaGetLastError());
     if (launches) ++*launches;
   }
+  return AT_OK;
+}
+
+int launch_splitk_finish(const GemmArgs& g_in, int splits, cudaStream_t stream, int64_t* launches) {
+  GemmArgs g = g_in;
+  if (g.M <= 0 || g.N <= 0 || splits < 1 || !g.partial || !g.C) return fail(AT_E_INVALID, "splitk_finish: bad arguments");
+  if (g.out_rows_per_batch <= 0) {
+    g.out_rows_per_batch = g.M;
+    g.out_batch_stride = 0;
+  }
+  if (!g.post) g.post_period = 1;
+  splitk_finish_kernel<<<grid_for(g.M * g.N, 256), 256, 0, stream>>>(g, splits);
+  AT_CUDA_TRY(cudaGetLastError());
+  if (launches) ++*launches;
+  return AT_OK;
+}
+
+int launch_merge_status(const uint32_t* status, uint32_t* flags, cudaStream_t stream, int64_t* launches) {
+  merge_status_kernel<<<1, 32, 0, stream>>>(status, flags);
+  AT_CUDA_TRY(cudaGetLastError());
+  if (launches) ++*launches;
   return AT_OK;
 }
 

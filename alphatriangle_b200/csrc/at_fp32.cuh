@@ -35,6 +35,8 @@ __host__ __device__ __forceinline__ float support_atom(int i, int atoms, float v
 }
 
 int launch_gemm(const GemmArgs& g, int splits, cudaStream_t stream, int64_t* launches);
+int launch_splitk_finish(const GemmArgs& g, int splits, cudaStream_t stream, int64_t* launches);
+int launch_merge_status(const uint32_t* status, uint32_t* flags, cudaStream_t stream, int64_t* launches);
 int launch_layernorm(const float* x, const float* w, const float* b, float* y, int64_t rows, int d, float eps,
                      int64_t out_rows_per_batch, int64_t out_batch_stride, int64_t ldy, cudaStream_t stream, int64_t* launches);
 int launch_attention(const float* qkv, float* out, int64_t boards, int L, int d, int heads, cudaStream_t stream, int64_t* launches);

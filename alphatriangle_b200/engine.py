@@ -159,6 +159,24 @@ class Engine:
         )
         return self._h_policy[:b].numpy(), self._h_value[:b].numpy(), int(self._h_flags[0].item())
 
+    def kernel_times(self) -> dict | None:
+        """Device milliseconds of the tower and FC kernels of the last bf16 evaluation (waits for it)."""
+        t, f = C.c_float(), C.c_float()
+        rc = self.lib.at_engine_kernel_ms(self.handle, C.byref(t), C.byref(f))
+        if rc != _lib.AT_OK:
+            return None
+        return {"tower_ms": float(t.value), "fc_ms": float(f.value)}
+
+    def bf16_trunk(self, packed: torch.Tensor) -> torch.Tensor:
+        """Test hook: first shared-FC activation [B, N] computed by the tcgen05 kernels."""
+        n = int(self.desc.shared_dims[0])
+        out = torch.empty((packed.shape[0], n), dtype=torch.float32, device=self.device)
+        _lib.check(
+            self.lib.at_engine_bf16_trunk(self.handle, _ptr(packed), packed.shape[0], _ptr(out), _stream_ptr(self.device)),
+            "at_engine_bf16_trunk",
+        )
+        return out
+
     def extract_features(self, packed: torch.Tensor, grid_channels: int, other_dim: int):
         """PackedState[B] on the device -> (grid [B,Cg,R,C], other [B,D]) on the device."""
         b = packed.shape[0]

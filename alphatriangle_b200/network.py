@@ -152,6 +152,8 @@ class NeuralNetwork:
     @staticmethod
     def _raise_for_flags(flags: int, batched: bool, what: str) -> None:
         pre = "batched input " if batched else "input "
+        if flags & _lib.FLAG_PIPELINE_TIMEOUT:
+            raise NetworkEvaluationError(f"tcgen05 pipeline wait timed out (status {(flags >> 8) & 0xFF:#x}){what}")
         if flags & _lib.FLAG_NONFINITE_GRID:
             raise NetworkEvaluationError(f"Non-finite values found in {pre}grid_tensor{what}")
         if flags & _lib.FLAG_NONFINITE_OTHER:

@@ -149,9 +149,18 @@ int at_engine_evaluate_packed(at_engine* e, int precision, const void* d_states,
 int at_engine_evaluate_host(at_engine* e, int precision, const void* h_states, int64_t batch, float* h_policy, float* h_value,
                             uint32_t* h_flags, void* stream);
 
-/* Introspection used by bench.py: kernels launched by the last evaluate call. */
+/* Introspection used by bench.py: kernels launched by the last evaluate call, and the
+ * device time (CUDA events on the launching stream) of the two tcgen05 kernels of the
+ * last bf16 evaluation; waits for that evaluation to finish. */
 int64_t at_engine_last_launches(const at_engine* e);
+int at_engine_kernel_ms(const at_engine* e, float* tower_ms, float* fc_ms);
+#define AT_FLAG_PIPELINE_TIMEOUT 0x80000000u /* a tcgen05 pipeline wait timed out (bits 8..15: which) */
 int at_engine_action_dim(const at_engine* e);
+
+/* Test hook: the bf16 path up to and including the first shared FC layer
+ * (tower + split-K FC + BatchNorm + activation, model.py:275-294), fp32 [B, FC_DIMS_SHARED[0]].
+ * Lets the parity tests localise an error to the tensor-core kernels. */
+int at_engine_bf16_trunk(at_engine* e, const void* d_states, int64_t batch, float* d_trunk, void* stream);
 
 /* ---- bring-up probe ------------------------------------------------------ */
 

@@ -73,13 +73,15 @@ def _encoder_layer(x, sd, base, heads, act):
     return x + ff
 
 
-def _mlp(x, sd, name, n_hidden, use_bn, act, has_out):
+def _mlp(x, sd, name, n_hidden, use_bn, act, has_out, taps=None):
     q = 0
     for _ in range(n_hidden):
         x = F.linear(x, sd[f"{name}.{q}.weight"], sd[f"{name}.{q}.bias"])
         if use_bn:
             x = _bn(x, sd, f"{name}.{q + 1}")
         x = act(x)
+        if taps is not None:
+            taps.append(x)
         q += 3 if use_bn else 2
     if has_out:
         x = F.linear(x, sd[f"{name}.{q}.weight"], sd[f"{name}.{q}.bias"])
@@ -87,8 +89,9 @@ def _mlp(x, sd, name, n_hidden, use_bn, act, has_out):
 
 
 @torch.no_grad()
-def forward(sd: dict, mc, grid: torch.Tensor, other: torch.Tensor):
-    """(policy_logits [B,A], value_logits [B,atoms]) in fp32 on the CPU."""
+def forward(sd: dict, mc, grid: torch.Tensor, other: torch.Tensor, taps: list | None = None):
+    """(policy_logits [B,A], value_logits [B,atoms]) in fp32 on the CPU. `taps`, if given, collects the
+    activation after each shared_fc layer."""
     act = _ACT[mc.ACTIVATION_FUNCTION]
     use_bn = mc.USE_BATCH_NORM
     x = grid
@@ -117,7 +120,7 @@ def forward(sd: dict, mc, grid: torch.Tensor, other: torch.Tensor):
         flat = seq.permute(1, 0, 2).flatten(1)
     else:
         flat = x.reshape(x.size(0), -1)
-    trunk = _mlp(torch.cat([flat, other], dim=1), sd, "shared_fc", len(mc.FC_DIMS_SHARED), use_bn, act, False)
+    trunk = _mlp(torch.cat([flat, other], dim=1), sd, "shared_fc", len(mc.FC_DIMS_SHARED), use_bn, act, False, taps)
     policy = _mlp(trunk, sd, "policy_head", len(mc.POLICY_HEAD_DIMS), use_bn, act, True)
     value = _mlp(trunk, sd, "value_head", len(mc.VALUE_HEAD_DIMS), use_bn, act, True)
     return policy, value

@@ -1,0 +1,94 @@
+"""tcgen05 / TMEM bf16 path parity (north_star: policy KL <= 1e-3 against the fp32 reference).
+Targets: the reference's recorded outputs (tests/golden) and the oracle on fresh states."""
+
+import numpy as np
+import pytest
+import torch
+from gpu_util import kl_rows, load_case, network
+
+from alphatriangle_b200 import _lib
+from alphatriangle_b200.packing import pack_states
+from alphatriangle_b200.synth import edge_states, synth_states
+from oracle import features_ref, model_ref
+
+pytestmark = pytest.mark.gpu
+
+KL_TOL = 1e-3      # north_star: policy KL(reference || ours) per state, bf16 path
+VALUE_TOL = 5e-2   # expected value, |ours - reference|; support spans [-10, 10], bf16 operands (8-bit mantissa)
+TRUNK_TOL = 3e-2   # first shared-FC activation, relative to its largest magnitude
+
+
+def test_bf16_path_is_available_for_the_baseline_config():
+    nn = network("conv_only", "bf16")
+    assert nn.precision == _lib.PREC_BF16 and nn.engine.supports(_lib.PREC_BF16)
+    assert network("conv_only", "auto").precision == _lib.PREC_BF16
+    # configurations outside the specialisation report why and stay on the fp32 path
+    odd = network("odd_gelu", "auto")
+    assert odd.precision == _lib.PREC_FP32 and not odd.engine.supports(_lib.PREC_BF16)
+
+
+def test_trunk_activation_matches_oracle(golden_dir):
+    mc, env, _seed, g = load_case("conv_only", golden_dir)
+    nn = network("conv_only", "bf16")
+    taps = []
+    model_ref.forward(nn.get_weights(), mc, torch.from_numpy(g["grid"]), torch.from_numpy(g["other"]), taps)
+    ref = taps[0].numpy()
+    got = nn.engine.bf16_trunk(torch.from_numpy(g["packed"]).cuda()).cpu().numpy()
+    scale = np.abs(ref).max()
+    assert np.abs(got - ref).max() <= TRUNK_TOL * scale, (np.abs(got - ref).max(), scale)
+
+
+def test_bf16_matches_reference_golden(golden_dir):
+    mc, env, _seed, g = load_case("conv_only", golden_dir)
+    nn = network("conv_only", "bf16")
+    probs, value = nn.evaluate_packed(torch.from_numpy(g["packed"]).cuda())
+    probs, value = probs.cpu().numpy(), value.cpu().numpy()
+    assert kl_rows(g["probs"], probs).max() <= KL_TOL
+    assert np.abs(value - g["values"]).max() <= VALUE_TOL
+    assert np.abs(probs.sum(axis=1) - 1.0).max() < 1e-5
+
+
+@pytest.mark.parametrize("batch", [1, 2, 3, 127, 129, 1000])
+def test_bf16_ragged_batches_match_oracle(batch, golden_dir):
+    """Odd board counts (a half-empty pair), partial 128-board FC tiles, single states."""
+    mc, env, _seed, _g = load_case("conv_only", golden_dir)
+    nn = network("conv_only", "bf16")
+    states = (synth_states(batch, env, seed=9000 + batch) + edge_states(env))[:batch]
+    grid, other = features_ref.extract_batch(states, mc)
+    torch.set_num_threads(8)
+    p_ref, v_ref = model_ref.evaluate_tensors(nn.get_weights(), mc, grid, other)
+    probs, value = nn.evaluate_packed(torch.from_numpy(pack_states(states, env)).cuda())
+    assert kl_rows(p_ref, probs.cpu().numpy()).max() <= KL_TOL
+    assert np.abs(value.cpu().numpy() - v_ref).max() <= VALUE_TOL
+
+
+def test_bf16_full_batch_rows_are_independent(golden_dir):
+    """At the BASELINE batch (4096): every board's result equals the result of the same board in a small
+    batch -- no cross-board leakage through the shared-memory images, TMEM or the FC tiles."""
+    mc, env, _seed, g = load_case("conv_only", golden_dir)
+    nn = network("conv_only", "bf16")
+    base = g["packed"]
+    packed = np.tile(base, (-(-4096 // base.shape[0]), 1))[:4096]
+    probs, value = nn.evaluate_packed(torch.from_numpy(packed).cuda())
+    p0, v0 = nn.evaluate_packed(torch.from_numpy(base).cuda())
+    idx = np.arange(4096) % base.shape[0]
+    # the tower is bitwise per board; only the split-K factor of the trunk FC depends on the batch size,
+    # so the two runs may differ by fp32 summation order and nothing more
+    assert np.abs(probs.cpu().numpy() - p0.cpu().numpy()[idx]).max() <= 1e-6
+    assert np.abs(value.cpu().numpy() - v0.cpu().numpy()[idx]).max() <= 1e-4
+
+
+def test_bf16_through_the_drop_in_api(golden_dir):
+    from golden_cases import case_states
+
+    mc, env, _seed, g = load_case("conv_only", golden_dir)
+    nn = network("conv_only", "bf16")
+    states = case_states("conv_only", env)[:16]
+    res = nn.evaluate_batch(states)
+    for i, (pol, val) in enumerate(res):
+        row = np.array([pol[a] for a in range(nn.action_dim)])
+        assert abs(row.sum() - 1.0) < 1e-5
+        assert kl_rows(g["probs"][i : i + 1], row[None, :]).max() <= KL_TOL
+        assert abs(val - float(g["values"][i])) <= VALUE_TOL
+    t = nn.engine.kernel_times()
+    assert t is not None and t["tower_ms"] > 0 and t["fc_ms"] > 0
