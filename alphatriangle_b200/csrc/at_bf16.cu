@@ -2,7 +2,7 @@
 //
 // tower_kernel  persistent, one CTA per SM, two boards in flight per CTA. A board's
 //               activations never leave shared memory between layers: they live as a
-//               zero-haloed 16-wide board image, [channel/8][162 rows][8 ch] bf16, so the
+//               zero-haloed 16-wide board image, [channel/8][17 zero + 128 rows][8 ch] bf16 (+17 zero), so the
 //               nine taps of a 3x3 convolution are nine ROW-SHIFTED views of one image and
 //               each tap/channel-block is one tcgen05.mma (M=128 padded positions, N=Cout,
 //               K=16) whose A descriptor merely starts 16*(dy*16+dx) bytes further on.
@@ -21,6 +21,7 @@
 
 #include <cuda_bf16.h>
 
+#include <cstdlib>
 #include <vector>
 
 #include "at_bf16.cuh"
@@ -37,12 +38,12 @@ using namespace umma;
 constexpr int kPadW = 16;                    // board row stride: cols + at least one shared zero column
 constexpr int kM = 128;                      // MMA rows = padded positions y*16 + x
 constexpr int kHalo = 17;                    // zero rows before / after: max |dy*16 + dx|
-constexpr int kImgRows = kM + 2 * kHalo;     // 162
-constexpr int kPlaneBytes = kImgRows * 16;   // one 8-channel plane: 162 rows x 16 B
+constexpr int kPlaneRows = kM + kHalo;       // 145: the trailing halo of one 8-channel plane is the leading halo of the next
+constexpr int kPlaneBytes = kPlaneRows * 16; // 2,320
 constexpr int kMaxCh = 128;
-constexpr int kBufBytes = (kMaxCh / 8) * kPlaneBytes;  // 41,472
+constexpr int kBufBytes = (kMaxCh / 8) * kPlaneBytes + kHalo * 16;  // 37,392: 16 planes + the last plane's trailing halo
 constexpr int kStageBytes = 16384;
-constexpr int kStages = 3;
+constexpr int kStages = 4;
 constexpr int kMaxLayers = 12;
 constexpr int kMaxSlabs = 32;                // weight slabs per layer (9 taps x 128 channels / 64 = 18 at the defaults)
 constexpr int kBoards = 2;                   // boards in flight per CTA
@@ -71,6 +72,7 @@ struct TowerParams {
   int n_kc;                // L * C_last / 8
   int rows, cols;
   uint32_t* status;
+  uint32_t debug;  // timing experiments only (AT_TOWER_DEBUG): 1 no weight copies, 2 no MMAs, 4 no epilogue math, 8 no layer 0
 };
 
 constexpr size_t tower_smem_bytes() {
@@ -96,6 +98,22 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 __device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
 __device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
 
+template <int ACT>
+__device__ __forceinline__ float act_fn(float x) {
+  if constexpr (ACT == AT_ACT_RELU) return fmaxf(x, 0.0f);
+  else return apply_act(x, ACT);
+}
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
+
+// ACT = the model-wide activation (every conv_block and ResidualBlock of a model shares it, model.py:127)
+template <int ACT>
 __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_constant__ TowerParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* ring = smem;
@@ -165,8 +183,12 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
           for (int s = 0; s < p.layers[l].n_slabs; ++s) {
             ok = wait_bar(bar_empty + 8 * stage, phase ^ 1, p.status, 1u);
             if (!ok) break;
-            mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
-            bulk_g2s(ring_u + stage * kStageBytes, src, bytes, bar_full + 8 * stage);
+            if (p.debug & 1u) {
+              mbar_arrive(bar_full + 8 * stage);
+            } else {
+              mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
+              bulk_g2s(ring_u + stage * kStageBytes, src, bytes, bar_full + 8 * stage);
+            }
             src += bytes;
             if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
@@ -210,8 +232,9 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
               for (int j = 0; j < mma_per_slab; ++j) {
                 const uint32_t a_lo = a_lo_fixed | (a_img16[b] + a_off16 + (uint32_t)j * (2 * kPlaneBytes >> 4));
                 const uint32_t b_lo = b_lo_fixed | (b16 + (uint32_t)j * 2 * b_lbo16);
-                mma_bf16(tmem_base + (uint32_t)b * 128, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo, idesc,
-                         (s | j) != 0);
+                if (!(p.debug & 2u))
+                  mma_bf16(tmem_base + (uint32_t)b * 128, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo, idesc,
+                           (s | j) != 0);
               }
             }
             mma_commit(bar_empty + 8 * stage);  // slab may be overwritten once these MMAs retire
@@ -229,14 +252,15 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     const int y = m / kPadW, x = m % kPadW;
     const bool inside = (y < p.rows) && (x < p.cols);
     const int pos = y * p.cols + x;  // compact position index (token order h*W + w)
-    uint8_t* my_act = act + (size_t)eb * 2 * kBufBytes;
+    const uint32_t my_act_u = act_u + (uint32_t)eb * 2 * kBufBytes + (uint32_t)(kHalo + m) * 16;  // this row, plane 0, buffer 0
+    const uint32_t tmem_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)eb * 128;
     uint32_t acc_phase = 0;
     bool ok = true;
     for (int64_t pair = blockIdx.x; pair < n_pairs && ok; pair += gridDim.x) {
       const int64_t board = pair * kBoards + eb;
       const bool valid = board < p.batch;
       // ---- layer 0 on CUDA cores, straight from the bitmasks (extractor.py:33-46 + conv_body.0) ----
-      {
+      if (!(p.debug & 8u)) {
         float g[9];
 #pragma unroll
         for (int t = 0; t < 9; ++t) g[t] = 0.0f;
@@ -252,18 +276,21 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
             }
           }
         }
-        uint8_t* dst = my_act + 0 * kBufBytes + (size_t)(kHalo + m) * 16;
+#pragma unroll 1
         for (int c8 = 0; c8 < p.c0; c8 += 8) {
-          float v[8];
+          const float4 ba = *reinterpret_cast<const float4*>(s_b0 + c8), bb = *reinterpret_cast<const float4*>(s_b0 + c8 + 4);
+          float v[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            float a = s_b0[c8 + j];
-#pragma unroll
-            for (int t = 0; t < 9; ++t) a = fmaf(g[t], s_w0[t * p.c0 + c8 + j], a);
-            v[j] = inside ? apply_act(a, p.act0) : 0.0f;
+          for (int t = 0; t < 9; ++t) {
+            const float4 wa = *reinterpret_cast<const float4*>(s_w0 + t * p.c0 + c8);
+            const float4 wb = *reinterpret_cast<const float4*>(s_w0 + t * p.c0 + c8 + 4);
+            v[0] = fmaf(g[t], wa.x, v[0]); v[1] = fmaf(g[t], wa.y, v[1]); v[2] = fmaf(g[t], wa.z, v[2]); v[3] = fmaf(g[t], wa.w, v[3]);
+            v[4] = fmaf(g[t], wb.x, v[4]); v[5] = fmaf(g[t], wb.y, v[5]); v[6] = fmaf(g[t], wb.z, v[6]); v[7] = fmaf(g[t], wb.w, v[7]);
           }
-          *reinterpret_cast<uint4*>(dst + (size_t)(c8 / 8) * kPlaneBytes) =
-              make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+#pragma unroll
+          for (int j = 0; j < 8; ++j) v[j] = inside ? act_fn<ACT>(v[j]) : 0.0f;
+          sts128(my_act_u + (uint32_t)(c8 / 8) * kPlaneBytes,
+                 make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7])));
         }
       }
       fence_proxy_async_smem();
@@ -277,32 +304,35 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         acc_phase ^= 1;
         tc_fence_after();
         const float* bias = s_bias + L.bias_slot * 128;
-        const uint8_t* res = L.res >= 0 ? my_act + (size_t)L.res * kBufBytes + (size_t)(kHalo + m) * 16 : nullptr;
-        for (int c0 = 0; c0 < L.cout; c0 += 32) {
+        const bool has_res = L.res >= 0;
+        const uint32_t res_u = my_act_u + (uint32_t)(has_res ? L.res : 0) * kBufBytes;
+        const bool to_smem = L.dst < 2;
+        const uint32_t dst_u = my_act_u + (uint32_t)(to_smem ? L.dst : 0) * kBufBytes;
+        uint8_t* gdst = p.fc_a + (((board >> 7) * p.n_kc + (int64_t)pos * (L.cout / 8)) * 128 + (board & 127)) * 16;
+        const bool gstore = valid && inside;
+        const int cout = (p.debug & 4u) ? 0 : L.cout;
+#pragma unroll 1
+        for (int c0 = 0; c0 < cout; c0 += 32) {
           uint32_t r[32];
-          tmem_ld32(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(eb * 128 + c0), r);
+          tmem_ld32(tmem_row + (uint32_t)c0, r);
           tmem_ld_wait();
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
-            float v[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = __uint_as_float(r[i * 8 + j]) + bias[c0 + i * 8 + j];
-            if (res) {
-              const uint4 rv = *reinterpret_cast<const uint4*>(res + (size_t)((c0 + i * 8) / 8) * kPlaneBytes);
+            const float4 ba = *reinterpret_cast<const float4*>(bias + c0 + i * 8), bb = *reinterpret_cast<const float4*>(bias + c0 + i * 8 + 4);
+            float v[8] = {__uint_as_float(r[i * 8 + 0]) + ba.x, __uint_as_float(r[i * 8 + 1]) + ba.y, __uint_as_float(r[i * 8 + 2]) + ba.z,
+                          __uint_as_float(r[i * 8 + 3]) + ba.w, __uint_as_float(r[i * 8 + 4]) + bb.x, __uint_as_float(r[i * 8 + 5]) + bb.y,
+                          __uint_as_float(r[i * 8 + 6]) + bb.z, __uint_as_float(r[i * 8 + 7]) + bb.w};
+            const int chunk = c0 / 8 + i;
+            if (has_res) {
+              const uint4 rv = lds128(res_u + (uint32_t)chunk * kPlaneBytes);
               v[0] += bf16_lo(rv.x); v[1] += bf16_hi(rv.x); v[2] += bf16_lo(rv.y); v[3] += bf16_hi(rv.y);
               v[4] += bf16_lo(rv.z); v[5] += bf16_hi(rv.z); v[6] += bf16_lo(rv.w); v[7] += bf16_hi(rv.w);
             }
 #pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = inside ? apply_act(v[j], L.act) : 0.0f;
+            for (int j = 0; j < 8; ++j) v[j] = inside ? act_fn<ACT>(v[j]) : 0.0f;
             const uint4 out = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
-            const int chunk = (c0 + i * 8) / 8;
-            if (L.dst < 2) {
-              *reinterpret_cast<uint4*>(my_act + (size_t)L.dst * kBufBytes + (size_t)chunk * kPlaneBytes + (size_t)(kHalo + m) * 16) = out;
-            } else if (valid && inside) {
-              const int64_t kc = (int64_t)pos * (L.cout / 8) + chunk;
-              uint8_t* gdst = p.fc_a + (((board >> 7) * p.n_kc + kc) * 128 + (board & 127)) * 16;
-              *reinterpret_cast<uint4*>(gdst) = out;
-            }
+            if (to_smem) sts128(dst_u + (uint32_t)chunk * kPlaneBytes, out);
+            else if (gstore) *reinterpret_cast<uint4*>(gdst + (size_t)chunk * 2048) = out;
           }
         }
         tc_fence_before();  // TMEM reads are done before the next layer's MMAs overwrite the accumulator
@@ -592,7 +622,11 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
     AT_CUDA_TRY(cudaMalloc(&b->status, 4 * sizeof(uint32_t)));
     AT_CUDA_TRY(cudaMemset(b->status, 0, 4 * sizeof(uint32_t)));
     for (auto& e : b->ev) AT_CUDA_TRY(cudaEventCreate(&e));
-    AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+    AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<AT_ACT_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+    AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<AT_ACT_GELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+    AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<AT_ACT_SILU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+    AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<AT_ACT_TANH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+    AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<AT_ACT_SIGMOID>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
     AT_CUDA_TRY(cudaFuncSetAttribute(fc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fc_smem_bytes()));
     return AT_OK;
   };
@@ -656,10 +690,20 @@ int bf16_trunk(Bf16Path* b, const Plan& p, const float* folded, int slot, const 
   tp.b0 = folded + b->b0_off;
   tp.fc_a = b->fc_a;
   tp.status = b->status;
+  {
+    const char* dbg = getenv("AT_TOWER_DEBUG");
+    tp.debug = dbg ? (uint32_t)atoi(dbg) : 0u;
+  }
   const int64_t n_pairs = (batch + kBoards - 1) / kBoards;
   const unsigned grid = (unsigned)(n_pairs < b->sms ? n_pairs : b->sms);
   AT_CUDA_TRY(cudaEventRecord(b->ev[0], st));
-  tower_kernel<<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp);
+  switch (tp.act0) {
+    case AT_ACT_RELU: tower_kernel<AT_ACT_RELU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
+    case AT_ACT_GELU: tower_kernel<AT_ACT_GELU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
+    case AT_ACT_SILU: tower_kernel<AT_ACT_SILU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
+    case AT_ACT_TANH: tower_kernel<AT_ACT_TANH><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
+    default: tower_kernel<AT_ACT_SIGMOID><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
+  }
   AT_CUDA_TRY(cudaGetLastError());
   AT_CUDA_TRY(cudaEventRecord(b->ev[1], st));
   ++*launches;

@@ -1,0 +1,29 @@
+"""Time the tower / FC kernels at one batch size (CUDA events inside the engine). Used for timing
+experiments (AT_TOWER_DEBUG) and as the short command ncu profiles."""
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+import torch
+
+sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
+import alphatriangle_b200 as at  # noqa: E402
+from alphatriangle_b200 import _lib  # noqa: E402
+from alphatriangle_b200.packing import pack_states  # noqa: E402
+from alphatriangle_b200.synth import synth_state_dict, synth_states  # noqa: E402
+
+B = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
+reps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
+env, mc = at.EnvConfig(), at.ModelConfig(USE_TRANSFORMER=False)
+nn = at.NeuralNetwork(mc, env, None, torch.device("cuda:0"), precision="bf16", max_batch=B)
+nn.set_weights(synth_state_dict(nn.get_weights(), 1))
+base = pack_states(synth_states(256, env, seed=5), env)
+packed = torch.from_numpy(np.tile(base, (-(-B // 256), 1))[:B]).cuda()
+ts = []
+for _ in range(reps):
+    nn.engine.evaluate_packed(packed, _lib.PREC_BF16)
+    ts.append(nn.engine.kernel_times())
+t = ts[-1]
+print(f"debug={os.environ.get('AT_TOWER_DEBUG', '0')} B={B} tower_ms={min(x['tower_ms'] for x in ts):.4f} fc_ms={t['fc_ms']:.4f} "
+      f"states/s(tower)={B / (min(x['tower_ms'] for x in ts) * 1e-3):.0f}")
