@@ -45,7 +45,7 @@ constexpr int kBufBytes = (kMaxCh / 8) * kPlaneBytes + kHalo * 16;  // 37,392: 1
 constexpr int kStageBytes = 16384;
 constexpr int kStages = 4;
 constexpr int kMaxLayers = 12;
-constexpr int kMaxSlabs = 32;                // weight slabs per layer (9 taps x 128 channels / 64 = 18 at the defaults)
+constexpr int kMaxSlabs = 36;                // weight slabs per layer (9 taps x 128 channels / 64 = 18 at the defaults)
 constexpr int kBoards = 2;                   // boards in flight per CTA
 constexpr int kTowerThreads = 64 + kBoards * 128;
 constexpr long long kTimeoutCycles = 2000000000LL;  // ~1 s: a wedged pipeline reports instead of hanging
@@ -56,6 +56,9 @@ struct TowerLayer {
   int act;
   int bias_slot;
   uint32_t slab_bytes;
+  // where each weight slab's first MMA reads its A operand, relative to the source image, >> 4: the slab covers channels
+  // [c0, c0 + ks) of one tap, i.e. plane c0/8 of the image shifted by (dy*16 + dx) rows
+  uint32_t aoff[kMaxSlabs];
 };
 
 struct TowerParams {
@@ -77,10 +80,17 @@ struct TowerParams {
 
 constexpr size_t tower_smem_bytes() {
   return (size_t)kStages * kStageBytes + (size_t)kBoards * 2 * kBufBytes + (size_t)kMaxLayers * 128 * 4 + 9 * 128 * 4 + 128 * 4 +
-         (size_t)kMaxLayers * kMaxSlabs * 4 + (2 * kStages + 2) * 8 + 16;
+         (2 * kStages + 2) * 8 + 16;
+}
+
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred P;\n\telect.sync _|P, 0xffffffff;\n\tselp.u32 %0, 1, 0, P;\n\t}" : "=r"(pred));
+  return pred != 0;
 }
 
 __device__ __forceinline__ bool wait_bar(uint32_t bar, uint32_t parity, uint32_t* status, uint32_t code) {
+  if (mbar_try_wait(bar, parity)) return true;  // common case: no clock reads on the fast path
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
     if (clock64() - t0 > kTimeoutCycles) {
@@ -112,6 +122,25 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   return v;
 }
 
+// One weight slab against both boards' images: NM K-steps of 16 channels each, A advancing two 8-channel planes per
+// step, B advancing two planes of the slab. Descriptor high words are constant (SBO = 128 B, version 1, no swizzle).
+template <int NM>
+__device__ __forceinline__ void issue_slab(uint32_t tmem_base, uint32_t a0_16, uint32_t a1_16, uint32_t b16, uint32_t a_lo_fixed,
+                                           uint32_t b_lo_fixed, uint32_t b_step16, uint32_t idesc, bool first) {
+  constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
+#pragma unroll
+  for (int b = 0; b < kBoards; ++b) {
+    const uint32_t a16 = b == 0 ? a0_16 : a1_16;
+#pragma unroll
+    for (int j = 0; j < NM; ++j) {
+      const uint32_t a_lo = a_lo_fixed | (a16 + (uint32_t)j * (2 * kPlaneBytes >> 4));
+      const uint32_t b_lo = b_lo_fixed | (b16 + (uint32_t)j * b_step16);
+      mma_bf16(tmem_base + (uint32_t)b * 128, ((uint64_t)kDescHi << 32) | a_lo, ((uint64_t)kDescHi << 32) | b_lo, idesc,
+               !(first && j == 0));
+    }
+  }
+}
+
 // ACT = the model-wide activation (every conv_block and ResidualBlock of a model shares it, model.py:127)
 template <int ACT>
 __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_constant__ TowerParams p) {
@@ -121,8 +150,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   float* s_bias = reinterpret_cast<float*>(act + kBoards * 2 * kBufBytes);  // [kMaxLayers][128]
   float* s_w0 = s_bias + kMaxLayers * 128;                            // [9][c0]
   float* s_b0 = s_w0 + 9 * 128;                                       // [c0]
-  uint32_t* s_aoff = reinterpret_cast<uint32_t*>(s_b0 + 128);          // [kMaxLayers][kMaxSlabs]: A start of each slab's first MMA, >> 4
-  uint64_t* bars = reinterpret_cast<uint64_t*>(s_aoff + kMaxLayers * kMaxSlabs);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(s_b0 + 128);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 2);
 
   const int tid = threadIdx.x, warp = tid / 32, lane = tid % 32;
@@ -135,20 +163,6 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   for (int i = tid; i < p.n_layers * 128; i += kTowerThreads) s_bias[i] = p.bias[i];
   for (int i = tid; i < 9 * p.c0; i += kTowerThreads) s_w0[i] = p.w0[i];
   for (int i = tid; i < p.c0; i += kTowerThreads) s_b0[i] = p.b0[i];
-  // Where each weight slab's first MMA reads its A operand, relative to the layer's source image: the slab covers
-  // channels [c0, c0 + ks) of one tap, i.e. plane c0/8 of the image, shifted by (dy*16 + dx) rows.
-  for (int i = tid; i < p.n_layers * kMaxSlabs; i += kTowerThreads) {
-    const TowerLayer& L = p.layers[i / kMaxSlabs];
-    const int sl = i % kMaxSlabs;
-    uint32_t off = 0;
-    if (sl < L.n_slabs) {
-      const int k0 = sl * L.ks;
-      const int tap = k0 / L.cin, c0 = k0 - tap * L.cin;
-      const int shift = L.taps == 9 ? (tap / 3 - 1) * kPadW + (tap % 3 - 1) : 0;
-      off = (uint32_t)((c0 / 8) * kPlaneBytes + (kHalo + shift) * 16) >> 4;
-    }
-    s_aoff[i] = off;
-  }
   if (tid == 0) {
     for (int i = 0; i < kStages; ++i) {
       mbar_init(bar_full + 8 * i, 1);
@@ -196,52 +210,47 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer: a single thread drives the tensor core =====
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0, act_phase = 0;
-      bool ok = true;
-      for (int64_t pair = blockIdx.x; pair < n_pairs && ok; pair += gridDim.x) {
-        for (int l = 0; l < p.n_layers && ok; ++l) {
-          const TowerLayer& L = p.layers[l];
-          ok = wait_bar(bar_act, act_phase, p.status, 2u);  // this layer's input images are written
+    // ===== MMA issuer: the warp stays converged; one elected lane issues tcgen05.mma / commit =====
+    int stage = 0;
+    uint32_t phase = 0, act_phase = 0;
+    bool ok = true;
+    const uint32_t a_lo_fixed = (uint32_t)(kPlaneBytes >> 4) << 16;  // LBO = one 8-channel plane
+    for (int64_t pair = blockIdx.x; pair < n_pairs && ok; pair += gridDim.x) {
+      for (int l = 0; l < p.n_layers && ok; ++l) {
+        const TowerLayer& L = p.layers[l];
+        ok = __all_sync(0xffffffffu, wait_bar(bar_act, act_phase, p.status, 2u));  // this layer's input images are written
+        if (!ok) break;
+        act_phase ^= 1;
+        tc_fence_after();
+        const uint32_t idesc = idesc_bf16(kM, (uint32_t)L.cout);
+        const uint32_t b_lbo16 = (uint32_t)L.cout;  // bytes between 8-channel planes of a slab, >> 4
+        const uint32_t b_lo_fixed = b_lbo16 << 16;
+        const int mma_per_slab = L.ks / 16;
+        const int n_slabs = L.n_slabs;
+        const uint32_t a0_img16 = (act_u + (uint32_t)(0 * 2 + L.src) * kBufBytes) >> 4;
+        const uint32_t a1_img16 = (act_u + (uint32_t)(1 * 2 + L.src) * kBufBytes) >> 4;
+        for (int s = 0; s < n_slabs; ++s) {
+          const uint32_t a_off16 = L.aoff[s];
+          ok = __all_sync(0xffffffffu, wait_bar(bar_full + 8 * stage, phase, p.status, 4u));
           if (!ok) break;
-          act_phase ^= 1;
           tc_fence_after();
-          const uint32_t idesc = idesc_bf16(kM, (uint32_t)L.cout);
-          const uint32_t b_lbo16 = (uint32_t)L.cout;  // bytes between 8-channel planes of a slab, >> 4
-          const int mma_per_slab = L.ks / 16;
-          const int n_slabs = L.n_slabs;
-          // descriptor halves that do not change inside the layer (see umma::smem_desc)
-          const uint32_t desc_hi = (128u >> 4) | (1u << 14);                       // SBO = 128 B, version 1, no swizzle
-          const uint32_t a_lo_fixed = (uint32_t)(kPlaneBytes >> 4) << 16;          // LBO = one 8-channel plane
-          const uint32_t b_lo_fixed = b_lbo16 << 16;
-          uint32_t a_img16[kBoards];
-#pragma unroll
-          for (int b = 0; b < kBoards; ++b) a_img16[b] = (act_u + (uint32_t)(b * 2 + L.src) * kBufBytes) >> 4;
-          const uint32_t* aoff = s_aoff + l * kMaxSlabs;
-          for (int s = 0; s < n_slabs; ++s) {
-            const uint32_t a_off16 = aoff[s];
-            ok = wait_bar(bar_full + 8 * stage, phase, p.status, 4u);
-            if (!ok) break;
-            tc_fence_after();
-            const uint32_t b16 = (ring_u + stage * kStageBytes) >> 4;
-#pragma unroll
-            for (int b = 0; b < kBoards; ++b) {
-#pragma unroll 4
-              for (int j = 0; j < mma_per_slab; ++j) {
-                const uint32_t a_lo = a_lo_fixed | (a_img16[b] + a_off16 + (uint32_t)j * (2 * kPlaneBytes >> 4));
-                const uint32_t b_lo = b_lo_fixed | (b16 + (uint32_t)j * 2 * b_lbo16);
-                if (!(p.debug & 2u))
-                  mma_bf16(tmem_base + (uint32_t)b * 128, ((uint64_t)desc_hi << 32) | a_lo, ((uint64_t)desc_hi << 32) | b_lo, idesc,
-                           (s | j) != 0);
-              }
+          const uint32_t b16 = (ring_u + stage * kStageBytes) >> 4;
+          if (elect_one()) {
+            if (!(p.debug & 2u)) {
+              if (mma_per_slab == 4)
+                issue_slab<4>(tmem_base, a0_img16 + a_off16, a1_img16 + a_off16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
+              else if (mma_per_slab == 2)
+                issue_slab<2>(tmem_base, a0_img16 + a_off16, a1_img16 + a_off16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
+              else
+                issue_slab<1>(tmem_base, a0_img16 + a_off16, a1_img16 + a_off16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
             }
             mma_commit(bar_empty + 8 * stage);  // slab may be overwritten once these MMAs retire
-            if (++stage == kStages) { stage = 0; phase ^= 1; }
           }
-          if (ok) mma_commit(bar_acc);  // both boards' accumulators are complete
+          __syncwarp();
+          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
+        if (ok && elect_one()) mma_commit(bar_acc);  // both boards' accumulators are complete
+        __syncwarp();
       }
     }
   } else {
@@ -541,6 +550,11 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
     if (c.sh != 1 || c.sw != 1 || !(k3 || (k1 && i > 0))) return no("convolutions must be 3x3 stride 1 pad 1 (or the 1x1 projection)");
     if (c.cout % 16 != 0 || c.cout > kMaxCh || (i > 0 && c.cin % 16 != 0)) return no("channel counts must be multiples of 16, at most 128");
     if (c.cout % 32 != 0) return no("channel counts must be multiples of 32");
+    if (i > 0) {
+      const int ks = c.cin >= 64 ? 64 : c.cin;
+      if ((ks != 16 && ks != 32 && ks != 64) || c.cin % ks != 0 || c.kh * c.kw * c.cin / ks > kMaxSlabs)
+        return no("input channel counts must be 16, 32 or a multiple of 64");
+    }
   }
   const Affine& fc = p.shared[0];
   if (fc.N % 32 != 0 || fc.N > 128) return no("first shared FC width must be a multiple of 32, at most 128");
@@ -564,9 +578,14 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
     TowerLayer& L = tp.layers[slot];
     L.cin = c.cin; L.cout = c.cout; L.taps = c.kh * c.kw;
     L.ks = c.cin >= 64 ? 64 : c.cin;
-    while ((L.taps * c.cin) % L.ks) L.ks /= 2;
     L.n_slabs = L.taps * c.cin / L.ks;
     L.slab_bytes = (uint32_t)L.ks * c.cout * 2;
+    for (int sl = 0; sl < L.n_slabs && sl < kMaxSlabs; ++sl) {
+      const int k0 = sl * L.ks;
+      const int tap = k0 / c.cin, ch0 = k0 - tap * c.cin;
+      const int shift = L.taps == 9 ? (tap / 3 - 1) * kPadW + (tap % 3 - 1) : 0;
+      L.aoff[sl] = (uint32_t)((ch0 / 8) * kPlaneBytes + (kHalo + shift) * 16) >> 4;
+    }
     L.src = src; L.dst = dst; L.res = res; L.act = c.f.act; L.bias_slot = slot;
     b->layer_wt.push_back(c.f.wt);
     b->layer_k.push_back(c.f.K);
