@@ -693,8 +693,8 @@ int bf16_pack_weights(Bf16Path* b, const Plan& p, const float* folded, int slot,
   return AT_OK;
 }
 
-int bf16_trunk(Bf16Path* b, const Plan& p, const float* folded, int slot, const void* d_states, int64_t batch, float* d_trunk,
-               cudaStream_t st, int64_t* launches) {
+int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slot, const void* d_states, int64_t batch, int* n_splits,
+                        cudaStream_t st, int64_t* launches) {
   const at_model_desc& d = p.d;
   // "other" features for the FC's last columns (the grid output of this launch is not used by the tower)
   AT_TRY(launch_features(d.env, 1, d.other_dim, d_states, batch, b->grid, b->other, st));
@@ -744,7 +744,17 @@ int bf16_trunk(Bf16Path* b, const Plan& p, const float* folded, int slot, const 
   ++*launches;
   b->timed = true;
 
-  // the FC's "other" columns in fp32 as one more partial, then bias + BatchNorm (folded) + activation
+  *n_splits = splits;
+  return AT_OK;
+}
+
+const float* bf16_partial(const Bf16Path* b) { return b->partial; }
+const float* bf16_other(const Bf16Path* b) { return b->other; }
+
+// Unfused tail of the trunk FC: the "other" columns in fp32 as one more partial, then bias + BatchNorm (folded) + activation.
+int bf16_finish_trunk(Bf16Path* b, const Plan& p, const float* folded, int splits, int64_t batch, float* d_trunk, cudaStream_t st,
+                      int64_t* launches) {
+  const at_model_desc& d = p.d;
   const Affine& fc = p.shared[0];
   GemmArgs o;
   o.A = b->other; o.lda = d.other_dim; o.M = batch; o.N = fc.N; o.K = d.other_dim;

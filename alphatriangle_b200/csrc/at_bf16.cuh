@@ -15,9 +15,15 @@ int bf16_create(const Plan& plan, int64_t max_batch, Bf16Path** out, std::string
 void bf16_destroy(Bf16Path* p);
 // folded fp32 set -> bf16 operand images for weight set `slot` (0/1)
 int bf16_pack_weights(Bf16Path* p, const Plan& plan, const float* d_folded, int slot, cudaStream_t stream);
-// PackedState[batch] -> activation of the first shared FC layer, fp32 [batch, shared[0].N]
-int bf16_trunk(Bf16Path* p, const Plan& plan, const float* d_folded, int slot, const void* d_states, int64_t batch, float* d_trunk,
-               cudaStream_t stream, int64_t* launches);
+// PackedState[batch] -> split-K partial sums of the first shared FC layer over the tower output, fp32
+// [n_splits][batch][shared[0].N] (bf16_partial), plus the "other" feature vectors (bf16_other)
+int bf16_trunk_partials(Bf16Path* p, const Plan& plan, const float* d_folded, int slot, const void* d_states, int64_t batch,
+                        int* n_splits, cudaStream_t stream, int64_t* launches);
+const float* bf16_partial(const Bf16Path* p);
+const float* bf16_other(const Bf16Path* p);
+// partials + other columns + bias, activation -> d_trunk fp32 [batch, shared[0].N] (unfused tail, also the test hook)
+int bf16_finish_trunk(Bf16Path* p, const Plan& plan, const float* d_folded, int n_splits, int64_t batch, float* d_trunk,
+                      cudaStream_t stream, int64_t* launches);
 const uint32_t* bf16_status_ptr(const Bf16Path* p);  // device word: non-zero if a pipeline wait timed out
 int bf16_kernel_ms(Bf16Path* p, float* tower_ms, float* fc_ms);
 

@@ -1,0 +1,35 @@
+// Fused trunk-finish + heads + softmax kernel (at_heads.cu).
+#pragma once
+
+#include "at_common.cuh"
+
+namespace at {
+
+struct HeadsParams {
+  // trunk FC: split-K partials [splits][batch][trunk_n], other features [batch][other_dim] against rows w_other [other_dim][trunk_n]
+  const float* partial;
+  int splits;
+  const float* other;
+  int other_dim;
+  const float* w_other;
+  const float* trunk_bias;
+  int trunk_n;
+  int act;
+  // heads: Wt [K][N] fp32 with folded BatchNorm, bias [N]
+  const float *wp1, *bp1, *wp2, *bp2;
+  const float *wv1, *bv1, *wv2, *bv2;
+  int pol_hidden, val_hidden, actions, atoms;
+  float v_min, v_max;
+  int64_t batch;
+  float* probs;
+  float* value;
+  uint32_t* flags;
+  int w_stage_off;         // filled by the launcher: float offset of the weight staging area in shared memory
+  const uint32_t* status;  // optional: tcgen05 pipeline status word folded into the flags
+};
+
+size_t heads_fused_smem(const HeadsParams& p);
+bool heads_fused_supported(const HeadsParams& p);
+int launch_heads_fused(const HeadsParams& p, cudaStream_t stream, int64_t* launches);
+
+}  // namespace at
