@@ -45,6 +45,7 @@ EXPORTS = (
     "at_engine_supports",
     "at_engine_forward",
     "at_engine_evaluate_packed",
+    "at_engine_evaluate_packed_static",
     "at_engine_evaluate_host",
     "at_engine_last_launches",
     "at_engine_kernel_ms",
@@ -117,6 +118,7 @@ def _bind(lib: C.CDLL) -> None:
         "at_engine_supports": (i32, [vp, i32]),
         "at_engine_forward": (i32, [vp, i32, vp, vp, i64, vp, vp, vp, vp]),
         "at_engine_evaluate_packed": (i32, [vp, i32, vp, i64, vp, vp, vp, vp]),
+        "at_engine_evaluate_packed_static": (i32, [vp, vp, i64, vp, vp, vp, vp]),
         "at_engine_evaluate_host": (i32, [vp, i32, vp, i64, vp, vp, vp, vp]),
         "at_engine_last_launches": (i64, [vp]),
         "at_engine_bf16_trunk": (i32, [vp, vp, i64, vp, vp]),

@@ -22,6 +22,7 @@
 #include <cuda_bf16.h>
 
 #include <cstdlib>
+#include <mutex>
 #include <vector>
 
 #include "at_bf16.cuh"
@@ -777,6 +778,78 @@ int bf16_kernel_ms(Bf16Path* b, float* tower_ms, float* fc_ms) {
   AT_CUDA_TRY(cudaEventElapsedTime(tower_ms, b->ev[0], b->ev[1]));
   AT_CUDA_TRY(cudaEventElapsedTime(fc_ms, b->ev[2], b->ev[3]));
   return AT_OK;
+}
+
+// ---- small-batch evaluation whose scratch is NOT allocated: one static device array -----------------------------
+//
+// at_engine_evaluate_packed_static (include/at_b200.h) runs the same kernels as the bf16 path above, but the memory
+// they use between themselves -- the "other" feature vectors, the tower's output tiles (the trunk FC's A operand) and
+// the FC's split-K partial sums -- is carved out of the array below instead of the engine's cudaMalloc'ed buffers.
+// Every GPU that loads this library carries the array (6 MiB) until the process exits, and every engine on that GPU
+// shares it.
+constexpr size_t kStaticScratchBytes = 6u << 20;
+static __device__ __align__(256) unsigned char g_static_scratch[kStaticScratchBytes];
+
+namespace {
+std::mutex g_static_mu;
+unsigned char* g_static_addr[64] = {};  // per device ordinal: device address of g_static_scratch, resolved once
+}  // namespace
+
+// In host code `g_static_scratch` is only a handle for the runtime, not a device address: a kernel handed that name
+// would fault (or, where the GPU can reach host memory, scribble over the wrong place). The address a kernel may use
+// comes from cudaGetSymbolAddress, asked once per device with that device current.
+static int static_scratch_base(unsigned char** out) {
+  int dev = 0;
+  AT_CUDA_TRY(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return fail(AT_E_INVALID, "static scratch: device ordinal out of range");
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_addr[dev]) {
+    void* ptr = nullptr;
+    AT_CUDA_TRY(cudaGetSymbolAddress(&ptr, g_static_scratch));
+    if (!ptr) return fail(AT_E_CUDA, "static scratch: cudaGetSymbolAddress returned a null address");
+    g_static_addr[dev] = static_cast<unsigned char*>(ptr);
+  }
+  *out = g_static_addr[dev];
+  return AT_OK;
+}
+
+int64_t bf16_static_max_batch() { return 128; }
+
+int bf16_trunk_partials_static(Bf16Path* b, const Plan& p, const float* folded, int slot, const void* d_states, int64_t batch,
+                               int* n_splits, const float** partial, const float** other, cudaStream_t st, int64_t* launches) {
+  const int64_t cap = bf16_static_max_batch();
+  if (batch > cap)
+    return fail(AT_E_INVALID, "at_engine_evaluate_packed_static: batch " + std::to_string(batch) + " exceeds the static scratch limit of " +
+                                  std::to_string(cap) + " states; use at_engine_evaluate_packed for larger batches");
+  auto up = [](size_t v) { return (v + 255) & ~size_t(255); };
+  const size_t need_fc_a = up((size_t)b->n_kc * 2048);  // one 128-board tile of A-operand chunks
+  const size_t need_partial = up((size_t)(b->max_splits + 1) * cap * b->fc_n * sizeof(float));
+  const size_t need_other = up((size_t)cap * p.d.other_dim * sizeof(float));
+  const size_t need_grid = up((size_t)cap * p.d.env.rows * p.d.env.cols * sizeof(float));
+  const size_t need = need_fc_a + need_partial + need_other + need_grid;
+  if (need > kStaticScratchBytes)
+    return fail(AT_E_UNSUPPORTED, "at_engine_evaluate_packed_static: this model needs " + std::to_string(need) +
+                                      " bytes of scratch, the static array holds " + std::to_string(kStaticScratchBytes));
+  unsigned char* base = nullptr;
+  AT_TRY(static_scratch_base(&base));
+  // Nothing in the array has to start at zero: rows < batch of every region are fully rewritten by the kernels before
+  // they are read, and rows >= batch (left over from earlier calls) only ever feed output rows that nobody reads.
+  uint8_t* const keep_fc_a = b->fc_a;
+  float* const keep_partial = b->partial;
+  float* const keep_other = b->other;
+  float* const keep_grid = b->grid;
+  b->fc_a = base;
+  b->partial = reinterpret_cast<float*>(base + need_fc_a);
+  b->other = reinterpret_cast<float*>(base + need_fc_a + need_partial);
+  b->grid = reinterpret_cast<float*>(base + need_fc_a + need_partial + need_other);
+  *partial = b->partial;
+  *other = b->other;
+  const int rc = bf16_trunk_partials(b, p, folded, slot, d_states, batch, n_splits, st, launches);
+  b->fc_a = keep_fc_a;
+  b->partial = keep_partial;
+  b->other = keep_other;
+  b->grid = keep_grid;
+  return rc;
 }
 
 }  // namespace at

@@ -24,6 +24,11 @@ const float* bf16_other(const Bf16Path* p);
 // partials + other columns + bias, activation -> d_trunk fp32 [batch, shared[0].N] (unfused tail, also the test hook)
 int bf16_finish_trunk(Bf16Path* p, const Plan& plan, const float* d_folded, int n_splits, int64_t batch, float* d_trunk,
                       cudaStream_t stream, int64_t* launches);
+// Same as bf16_trunk_partials with every intermediate buffer inside the library's static device array
+// (no allocation, batch <= bf16_static_max_batch()); *partial / *other point into that array.
+int64_t bf16_static_max_batch();
+int bf16_trunk_partials_static(Bf16Path* p, const Plan& plan, const float* d_folded, int slot, const void* d_states, int64_t batch,
+                               int* n_splits, const float** partial, const float** other, cudaStream_t stream, int64_t* launches);
 const uint32_t* bf16_status_ptr(const Bf16Path* p);  // device word: non-zero if a pipeline wait timed out
 int bf16_kernel_ms(Bf16Path* p, float* tower_ms, float* fc_ms);
 

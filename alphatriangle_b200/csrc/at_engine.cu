@@ -445,6 +445,41 @@ int at_engine_bf16_trunk(at_engine* e, const void* d_states, int64_t batch, floa
   return end_eval(e, st);
 }
 
+int at_engine_evaluate_packed_static(at_engine* e, const void* d_states, int64_t batch, float* d_policy, float* d_value,
+                                     uint32_t* d_flags, void* stream) {
+  if (!e) return fail(AT_E_INVALID, "at_engine_evaluate_packed_static: null engine");
+  if (batch < 0) return fail(AT_E_INVALID, "at_engine_evaluate_packed_static: negative batch");
+  if (batch == 0) return AT_OK;
+  if (!d_states || !d_policy || !d_value || !d_flags) return fail(AT_E_INVALID, "at_engine_evaluate_packed_static: null pointer");
+  if ((reinterpret_cast<uintptr_t>(d_states) & 15u) != 0)
+    return fail(AT_E_INVALID, "at_engine_evaluate_packed_static: d_states must be 16-byte aligned");
+  AT_TRY(check_precision(e, AT_PREC_BF16));
+  const Plan& p = e->plan;
+  if (!(p.shared.size() == 1 && p.policy.size() == 2 && p.value.size() == 2))
+    return fail(AT_E_UNSUPPORTED, "at_engine_evaluate_packed_static: needs one shared FC layer and one hidden layer per head");
+  DeviceGuard guard(e->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const float* W = nullptr;
+  AT_TRY(begin_eval(e, st, &W));
+  int splits = 0;
+  const float *partial = nullptr, *other = nullptr;
+  AT_TRY(bf16_trunk_partials_static(e->bf16, p, W, e->active, d_states, batch, &splits, &partial, &other, st, &e->last_launches));
+  const Affine& fc = p.shared[0];
+  HeadsParams hp{};
+  hp.partial = partial; hp.splits = splits;
+  hp.other = other; hp.other_dim = p.d.other_dim;
+  hp.w_other = W + fc.wt + (int64_t)p.flat * fc.N; hp.trunk_bias = W + fc.bias; hp.trunk_n = fc.N; hp.act = fc.act;
+  hp.wp1 = W + p.policy[0].wt; hp.bp1 = W + p.policy[0].bias; hp.wp2 = W + p.policy[1].wt; hp.bp2 = W + p.policy[1].bias;
+  hp.wv1 = W + p.value[0].wt; hp.bv1 = W + p.value[0].bias; hp.wv2 = W + p.value[1].wt; hp.bv2 = W + p.value[1].bias;
+  hp.pol_hidden = p.policy[0].N; hp.val_hidden = p.value[0].N; hp.actions = p.action_dim; hp.atoms = p.d.num_atoms;
+  hp.v_min = p.d.v_min; hp.v_max = p.d.v_max; hp.batch = batch;
+  hp.probs = d_policy; hp.value = d_value; hp.flags = d_flags; hp.status = bf16_status_ptr(e->bf16);
+  if (!heads_fused_supported(hp))
+    return fail(AT_E_UNSUPPORTED, "at_engine_evaluate_packed_static: head widths outside what the fused head kernel covers");
+  AT_TRY(launch_heads_fused(hp, st, &e->last_launches));
+  return end_eval(e, st);
+}
+
 int at_engine_forward(at_engine* e, int precision, const float* d_grid, const float* d_other, int64_t batch, float* d_policy,
                       float* d_value, uint32_t* d_flags, void* stream) {
   if (!e) return fail(AT_E_INVALID, "at_engine_forward: null engine");

@@ -143,6 +143,28 @@ int at_engine_forward(at_engine* e, int precision, const float* d_grid, const fl
 int at_engine_evaluate_packed(at_engine* e, int precision, const void* d_states, int64_t batch, float* d_policy, float* d_value,
                               uint32_t* d_flags, void* stream);
 
+/* No counterpart in the reference. at_engine_evaluate_packed for up to 128 states (four default MCTS leaf
+ * batches) on the bf16 path, for hosts that must not allocate device memory once they are running:
+ *   - a self-play process that shares its GPU with the trainer, where a cudaMalloc / cudaFree in the search loop
+ *     would synchronise the whole device and stall the trainer's streams, or fail once the trainer has taken the rest
+ *     of the memory;
+ *   - a league / old-vs-new evaluator holding many engines (one per model version): created with max_batch = 1 they
+ *     keep their weights and a minimum of private scratch, and all of them evaluate through this call.
+ * The buffers the kernels pass to each other (other-feature vectors, the tower's output tiles, the trunk FC's split-K
+ * partial sums; about 5.1 MB at the default configuration) live in ONE 6 MiB static device array inside the library
+ * instead of engine-owned allocations; the call itself allocates nothing (no cudaMalloc / cudaFree, no allocating
+ * library routine). Inputs and outputs are still the caller's.
+ *   - batch > 128, or a model whose scratch exceeds 6 MiB, is refused with an error (AT_E_INVALID / AT_E_UNSUPPORTED);
+ *     it is not limited by the engine's max_batch.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress): make that first
+ *     call before starting any stream capture.
+ *   - Every engine and every call on a GPU share the array and it keeps the previous call's bytes. Nothing in it needs
+ *     clearing (each call rewrites all rows it later reads), but two calls whose kernels overlap on the GPU -- different
+ *     streams, threads or engines -- race on it: serialise them (one stream, or events).
+ *   - Needs the bf16 path and the fused-head shape (one shared FC layer, one hidden layer per head). */
+int at_engine_evaluate_packed_static(at_engine* e, const void* d_states, int64_t batch, float* d_policy, float* d_value,
+                                     uint32_t* d_flags, void* stream);
+
 /* Same with HOST buffers (pinned memory recommended): copies the states in,
  * evaluates, copies probs / values / flags out and waits. This is the call a
  * host application (trimcts-style batcher) makes. */
