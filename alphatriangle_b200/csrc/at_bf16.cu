@@ -48,7 +48,9 @@ constexpr int kStages = 4;
 constexpr int kMaxLayers = 12;
 constexpr int kMaxSlabs = 36;                // weight slabs per layer (9 taps x 128 channels / 64 = 18 at the defaults)
 constexpr int kBoards = 2;                   // boards in flight per CTA
-constexpr int kTowerThreads = 64 + kBoards * 128;
+constexpr int kEpiSplit = 2;                 // epilogue warps per (board, TMEM lane quarter): each takes 1/kEpiSplit of the channels
+constexpr int kEpiWarps = kBoards * 4 * kEpiSplit;
+constexpr int kTowerThreads = 64 + kEpiWarps * 32;
 constexpr long long kTimeoutCycles = 2000000000LL;  // ~1 s: a wedged pipeline reports instead of hanging
 
 struct TowerLayer {
@@ -170,7 +172,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
       mbar_init(bar_empty + 8 * i, 1);
     }
     mbar_init(bar_acc, 1);
-    mbar_init(bar_act, kBoards * 4);  // one arrival per epilogue warp
+    mbar_init(bar_act, kEpiWarps);  // one arrival per epilogue warp
     fence_mbar_init();
   }
   if (warp == 0) {
@@ -256,8 +258,9 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     }
   } else {
     // ===== epilogue warps: 4 per board; warp%4 selects the TMEM lane quarter =====
-    const int eb = (warp - 2) / 4;
-    const int q = warp % 4;
+    const int eb = (warp - 2) / (4 * kEpiSplit);   // board of the pair
+    const int eh = ((warp - 2) / 4) % kEpiSplit;   // which share of the channels
+    const int q = warp % 4;                        // TMEM lane quarter this warp may read
     const int m = q * 32 + lane;  // padded position = MMA row = TMEM lane
     const int y = m / kPadW, x = m % kPadW;
     const bool inside = (y < p.rows) && (x < p.cols);
@@ -287,7 +290,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
           }
         }
 #pragma unroll 1
-        for (int c8 = 0; c8 < p.c0; c8 += 8) {
+        for (int c8 = eh * 8; c8 < p.c0; c8 += 8 * kEpiSplit) {
           const float4 ba = *reinterpret_cast<const float4*>(s_b0 + c8), bb = *reinterpret_cast<const float4*>(s_b0 + c8 + 4);
           float v[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
 #pragma unroll
@@ -322,7 +325,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         const bool gstore = valid && inside;
         const int cout = (p.debug & 4u) ? 0 : L.cout;
 #pragma unroll 1
-        for (int c0 = 0; c0 < cout; c0 += 32) {
+        for (int c0 = eh * 32; c0 < cout; c0 += 32 * kEpiSplit) {
           uint32_t r[32];
           tmem_ld32(tmem_row + (uint32_t)c0, r);
           tmem_ld_wait();

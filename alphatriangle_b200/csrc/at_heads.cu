@@ -28,7 +28,7 @@ constexpr int MAXV = (KC * MAXP * 128 / 4 + kThreads - 1) / kThreads;  // float4
 // Weights go global -> registers -> shared in chunks of KC rows, double-buffered so the next chunk's loads are in
 // flight while the current one is consumed. Warp w computes boards 4w..4w+3 (their A rows are warp-wide broadcast
 // float4 loads), lane l the outputs 4l..4l+3 of each 128-wide pass. Needs K % 4 == 0 and lda % 4 == 0.
-__device__ __forceinline__ void block_gemm(const float* __restrict__ A_s, int lda, int K, const float* __restrict__ Wt,
+__device__ __noinline__ void block_gemm(const float* __restrict__ A_s, int lda, int K, const float* __restrict__ Wt,
                                            const float* __restrict__ bias, int N, float* __restrict__ C_s, int ldc, int act,
                                            float* __restrict__ Ws) {
   const int tid = threadIdx.x, warp = tid / 32, lane = tid % 32;

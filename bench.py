@@ -33,6 +33,9 @@ sys.path.insert(0, str(ROOT))
 METRIC = "leaf evals/sec (states/sec) at batch 4096"
 UNIT = "states/s"
 FLOP_PER_STATE = {"conv_only": 167_855_872, "default_tf": 245_516_032}  # 2 FLOP/MAC, no padding credited
+# dram__bytes_read.sum + dram__bytes_write.sum of tower_kernel from the `ncu --set full` capture in profiles/ (per launch, batch 4096):
+# 1.73 MB read + 72.0 MB written (the 126 MB of FC operand tiles it produces mostly stay in the 126 MB L2)
+TOWER_DRAM_BYTES_PER_LAUNCH = {4096: 73_733_376}
 TOWER_FLOP_PER_STATE = 163_745_280  # conv_body + res_body only (69,120 + 4,423,680 + 17,694,720 + 4 x 35,389,440)
 WORKLOADS = {
     "conv_only": "conv-only AlphaTriangleNet (USE_TRANSFORMER=False), 8x15x3 env, batch 4096 synthetic states per GPU, features+forward",
@@ -291,7 +294,7 @@ def run_ours(args):
                     "api": "at_engine_evaluate_host (pinned host buffers)"},
             "gpu_launches": int(launches_per_step * args.steps),
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                         "traffic": None, "kernel": (kern or {}).get("name", "whole step (all kernels of the path)"),
+                         "traffic": TOWER_DRAM_BYTES_PER_LAUNCH.get(B) if kern else None, "kernel": (kern or {}).get("name", "whole step (all kernels of the path)"),
                          "kernel_ms": (kern or {}).get("ms"), "fc_kernel_ms": (kern or {}).get("fc_ms"),
                          "kernel_share_of_step": (kern or {}).get("share_of_step"),
                          "peak_source": f"{peaks['source']} bf16 dense, {'sustained' if peak == peaks['sustained'] else 'burst'}",
