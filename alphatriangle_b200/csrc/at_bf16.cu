@@ -129,7 +129,8 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 // step, B advancing two planes of the slab. Descriptor high words are constant (SBO = 128 B, version 1, no swizzle).
 template <int NM>
 __device__ __forceinline__ void issue_slab(uint32_t tmem_base, uint32_t a0_16, uint32_t a1_16, uint32_t b16, uint32_t a_lo_fixed,
-                                           uint32_t b_lo_fixed, uint32_t b_step16, uint32_t idesc, bool first) {
+                                           uint32_t b_lo_fixed, uint32_t b_step16, uint32_t idesc, bool first,
+                                           uint32_t tmem_board_stride = 128) {
   constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
 #pragma unroll
   for (int b = 0; b < kBoards; ++b) {
@@ -138,7 +139,7 @@ __device__ __forceinline__ void issue_slab(uint32_t tmem_base, uint32_t a0_16, u
     for (int j = 0; j < NM; ++j) {
       const uint32_t a_lo = a_lo_fixed | (a16 + (uint32_t)j * (2 * kPlaneBytes >> 4));
       const uint32_t b_lo = b_lo_fixed | (b16 + (uint32_t)j * b_step16);
-      mma_bf16(tmem_base + (uint32_t)b * 128, ((uint64_t)kDescHi << 32) | a_lo, ((uint64_t)kDescHi << 32) | b_lo, idesc,
+      mma_bf16(tmem_base + (uint32_t)b * tmem_board_stride, ((uint64_t)kDescHi << 32) | a_lo, ((uint64_t)kDescHi << 32) | b_lo, idesc,
                !(first && j == 0));
     }
   }
@@ -493,6 +494,8 @@ __global__ void gather_bias_kernel(const float* __restrict__ folded, const int64
   for (int i = threadIdx.x; i < 128; i += blockDim.x) dst[l * 128 + i] = i < widths[l] ? folded[offs[l] + i] : 0.0f;
 }
 
+#include "at_bf16_tf.inc"
+
 }  // namespace
 
 // ---- host side ---------------------------------------------------------------------------------
@@ -525,6 +528,12 @@ struct Bf16Path {
   int sms = 148;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // tower begin/end, fc begin/end
   bool timed = false;
+  // transformer extension (tower_tf_kernel)
+  bool tf = false;
+  TowerTfParams ttp{};
+  float* tfp[2] = {nullptr, nullptr};
+  int tfp_floats = 0;
+  size_t conv_stream_bytes = 0;
 };
 
 int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* reason) {
@@ -534,7 +543,12 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
     *reason = why;
     return AT_OK;
   };
-  if (p.transformer) return no("transformer layers are not on the tcgen05 path yet");
+  if (p.transformer) {
+    if (p.has_input_proj || d.t_dim != kTfD || p.cnn_ch != kTfD) return no("transformer on the tcgen05 path needs TRANSFORMER_DIM = last conv channels = 128");
+    if (d.t_heads * kTfDh != kTfD) return no("transformer on the tcgen05 path needs head width 32");
+    if (d.t_ff % 128 != 0 || d.t_ff > 1024) return no("TRANSFORMER_FC_DIM must be a multiple of 128, at most 1024");
+    if (d.t_layers > kMaxTfLayers) return no("at most 4 transformer layers on the tcgen05 path");
+  }
   if (d.grid_channels != 1) return no("GRID_INPUT_CHANNELS must be 1");
   if (d.env.rows * kPadW > kM || d.env.cols + 1 > kPadW) return no("board must fit a 16-wide, 128-position padded image (ROWS <= 8, COLS <= 15)");
   if (p.convs.empty()) return no("needs at least one conv_body layer");
@@ -619,6 +633,56 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
   b->fc_flat = p.flat;
   b->fc_wt = fc.wt;
   b->max_batch = max_batch;
+  b->conv_stream_bytes = b->wstream_bytes;
+  if (p.transformer) {
+    if (c_last != kTfD) {
+      delete b;
+      return no("last convolution must have 128 channels for the transformer path");
+    }
+    b->tf = true;
+    TowerTfParams& t = b->ttp;
+    t.t_layers = d.t_layers;
+    t.heads = d.t_heads;
+    t.ff_halves = d.t_ff / 128;
+    tp.layers[tp.n_layers - 1].dst = 3;  // becomes the residual stream x in tensor memory
+    int n = 0;
+    auto slab = [&](uint32_t bytes) {
+      if (n < kMaxRingSlabs) t.slab16[n] = (uint16_t)(bytes / 16);
+      ++n;
+    };
+    for (int l = 0; l < tp.n_layers; ++l)
+      for (int sl = 0; sl < tp.layers[l].n_slabs; ++sl) slab(tp.layers[l].slab_bytes);
+    int off = 0;
+    auto take = [&](int count) {
+      const int at0 = off;
+      off += (count + 3) & ~3;
+      return at0;
+    };
+    for (int l = 0; l < d.t_layers; ++l) {
+      for (int h = 0; h < d.t_heads; ++h) {
+        if (h > 0) slab(kTfD * kTfDh * 2);                    // out_proj columns of head h-1
+        slab(3 * kTfDh * 64 * 2); slab(3 * kTfDh * 64 * 2);   // fused q|k|v projection of head h, two K halves
+      }
+      slab(kTfD * kTfDh * 2);
+      for (int f = 0; f < t.ff_halves; ++f) {
+        if (f > 0) { slab(128 * 64 * 2); slab(128 * 64 * 2); }  // linear2, hidden half f-1
+        slab(128 * 64 * 2); slab(128 * 64 * 2);                 // linear1, hidden half f
+      }
+      slab(128 * 64 * 2); slab(128 * 64 * 2);
+      b->wstream_bytes += (size_t)d.t_heads * (3 * kTfDh * kTfD + kTfD * kTfDh) * 2 + (size_t)t.ff_halves * 2 * 128 * 128 * 2;
+      TfLayerOffsets& o = t.tl[l];
+      o.ln1_w = take(kTfD); o.ln1_b = take(kTfD); o.bq = take(kTfD); o.bk = take(kTfD); o.bv = take(kTfD); o.bout = take(kTfD);
+      o.ln2_w = take(kTfD); o.ln2_b = take(kTfD); o.b1 = take(d.t_ff); o.b2 = take(kTfD);
+    }
+    t.lnf_w = take(kTfD);
+    t.lnf_b = take(kTfD);
+    b->tfp_floats = off;
+    t.n_ring_slabs = n;
+    if (n > kMaxRingSlabs) {
+      delete b;
+      return no("too many weight slabs per board for the fused tower + transformer kernel");
+    }
+  }
 
   cudaDeviceProp prop;
   int dev = 0;
@@ -633,6 +697,10 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
       AT_CUDA_TRY(cudaMalloc(&b->wfc[i], (size_t)p.flat * fc.N * 2));
       AT_CUDA_TRY(cudaMalloc(&b->bias[i], (size_t)kMaxLayers * 128 * sizeof(float)));
     }
+    if (b->tf)
+      for (int i = 0; i < 2; ++i) AT_CUDA_TRY(cudaMalloc(&b->tfp[i], (size_t)b->tfp_floats * sizeof(float)));
+    AT_CUDA_TRY(cudaFuncSetAttribute(tower_tf_kernel<AT_ACT_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+    AT_CUDA_TRY(cudaFuncSetAttribute(tower_tf_kernel<AT_ACT_GELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
     AT_CUDA_TRY(cudaMalloc(&b->d_bias_off, kMaxLayers * sizeof(int64_t)));
     AT_CUDA_TRY(cudaMalloc(&b->d_bias_w, kMaxLayers * sizeof(int)));
     AT_CUDA_TRY(cudaMemcpy(b->d_bias_off, b->bias_off.data(), b->bias_off.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
@@ -668,6 +736,7 @@ void bf16_destroy(Bf16Path* b) {
     cudaFree(b->wstream[i]);
     cudaFree(b->wfc[i]);
     cudaFree(b->bias[i]);
+    cudaFree(b->tfp[i]);
   }
   cudaFree(b->d_bias_off);
   cudaFree(b->d_bias_w);
@@ -693,7 +762,42 @@ int bf16_pack_weights(Bf16Path* b, const Plan& p, const float* folded, int slot,
   AT_CUDA_TRY(cudaGetLastError());
   gather_bias_kernel<<<(unsigned)b->layer_wt.size(), 128, 0, st>>>(folded, b->d_bias_off, b->d_bias_w, (int)b->layer_wt.size(), b->bias[slot]);
   AT_CUDA_TRY(cudaGetLastError());
-  (void)p;
+  if (b->tf) {
+    const at_model_desc& d = p.d;
+    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(b->wstream[slot] + b->conv_stream_bytes);
+    auto pack = [&](const float* wt, const PackSel& sel) -> int {
+      pack_sel_kernel<<<64, 256, 0, st>>>(wt, sel, dst);
+      AT_CUDA_TRY(cudaGetLastError());
+      dst += (size_t)sel.n_rows * sel.k_count;
+      return AT_OK;
+    };
+    auto vec = [&](int dst_off, int64_t src_off, int n, float scale) -> int {
+      copy_scaled_kernel<<<4, 128, 0, st>>>(folded + src_off, b->tfp[slot] + dst_off, n, scale);
+      AT_CUDA_TRY(cudaGetLastError());
+      return AT_OK;
+    };
+    const float qscale = 1.0f / sqrtf((float)kTfDh);
+    const int halves = d.t_ff / 128;
+    for (int l = 0; l < d.t_layers; ++l) {
+      const EncoderLayer& e = p.enc[l];
+      for (int h = 0; h < d.t_heads; ++h) {
+        AT_TRY(pack(folded + e.qkv.wt, PackSel{3 * kTfDh, kTfD, 0, 3 * kTfD, kTfDh, {h * kTfDh, kTfD + h * kTfDh, 2 * kTfD + h * kTfDh}, qscale}));
+        AT_TRY(pack(folded + e.out.wt, PackSel{kTfD, kTfDh, h * kTfDh, kTfD, kTfD, {0, 0, 0}, 1.0f}));
+      }
+      for (int f = 0; f < halves; ++f) {
+        AT_TRY(pack(folded + e.ff1.wt, PackSel{128, kTfD, 0, d.t_ff, 128, {f * 128, 0, 0}, 1.0f}));
+        AT_TRY(pack(folded + e.ff2.wt, PackSel{kTfD, 128, f * 128, kTfD, kTfD, {0, 0, 0}, 1.0f}));
+      }
+      const TfLayerOffsets& o = b->ttp.tl[l];
+      AT_TRY(vec(o.ln1_w, e.ln1_w, kTfD, 1.0f)); AT_TRY(vec(o.ln1_b, e.ln1_b, kTfD, 1.0f));
+      AT_TRY(vec(o.bq, e.qkv.bias, kTfD, qscale)); AT_TRY(vec(o.bk, e.qkv.bias + kTfD, kTfD, 1.0f));
+      AT_TRY(vec(o.bv, e.qkv.bias + 2 * kTfD, kTfD, 1.0f)); AT_TRY(vec(o.bout, e.out.bias, kTfD, 1.0f));
+      AT_TRY(vec(o.ln2_w, e.ln2_w, kTfD, 1.0f)); AT_TRY(vec(o.ln2_b, e.ln2_b, kTfD, 1.0f));
+      AT_TRY(vec(o.b1, e.ff1.bias, d.t_ff, 1.0f)); AT_TRY(vec(o.b2, e.ff2.bias, kTfD, 1.0f));
+    }
+    AT_TRY(vec(b->ttp.lnf_w, p.lnf_w, kTfD, 1.0f));
+    AT_TRY(vec(b->ttp.lnf_b, p.lnf_b, kTfD, 1.0f));
+  }
   return AT_OK;
 }
 
@@ -720,6 +824,14 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
   const int64_t n_pairs = (batch + kBoards - 1) / kBoards;
   const unsigned grid = (unsigned)(n_pairs < b->sms ? n_pairs : b->sms);
   AT_CUDA_TRY(cudaEventRecord(b->ev[0], st));
+  if (b->tf) {
+    TowerTfParams t = b->ttp;
+    t.conv = tp;
+    t.tfp = b->tfp[slot];
+    t.pe = folded + p.pe;
+    if (tp.act0 == AT_ACT_RELU) tower_tf_kernel<AT_ACT_RELU><<<grid, kTfThreads, tower_smem_bytes(), st>>>(t);
+    else tower_tf_kernel<AT_ACT_GELU><<<grid, kTfThreads, tower_smem_bytes(), st>>>(t);
+  } else
   switch (tp.act0) {
     case AT_ACT_RELU: tower_kernel<AT_ACT_RELU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
     case AT_ACT_GELU: tower_kernel<AT_ACT_GELU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;

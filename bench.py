@@ -36,7 +36,9 @@ FLOP_PER_STATE = {"conv_only": 167_855_872, "default_tf": 245_516_032}  # SURVEY
 # dram__bytes_read.sum + dram__bytes_write.sum of tower_kernel from the `ncu --set full` capture in profiles/ (per launch, batch 4096):
 # 1.73 MB read + 72.0 MB written (the 126 MB of FC operand tiles it produces mostly stay in the 126 MB L2)
 TOWER_DRAM_BYTES_PER_LAUNCH = {4096: 73_733_376}
-TOWER_FLOP_PER_STATE = 163_745_280  # conv_body + res_body only (69,120 + 4,423,680 + 17,694,720 + 4 x 35,389,440)
+# dominant kernel's own algorithmic FLOPs: conv_body + res_body (69,120 + 4,423,680 + 17,694,720 + 4 x 35,389,440), plus the two
+# encoder layers (2 x 38,830,080) when they are fused into it
+TOWER_FLOP_PER_STATE = {"conv_only": 163_745_280, "default_tf": 163_745_280 + 77_660_160}
 WORKLOADS = {
     "conv_only": "conv-only AlphaTriangleNet (USE_TRANSFORMER=False), 8x15x3 env, batch 4096 synthetic states per GPU, features+forward",
     "default_tf": "default AlphaTriangleNet (2 transformer layers), 8x15x3 env, synthetic states, features+forward",
@@ -276,8 +278,9 @@ def run_ours(args):
         if tower_ms:
             # dominant kernel = the convolution tower; its own CUDA-event time, averaged over a second pass of K steps
             t_ms = sum(tower_ms) / len(tower_ms)
-            achieved = TOWER_FLOP_PER_STATE * B / (t_ms * 1e-3) / 1e12
-            kern = {"name": "tower_kernel (conv_body + res_body, tcgen05)", "ms": t_ms, "fc_ms": sum(fc_ms) / len(fc_ms),
+            achieved = TOWER_FLOP_PER_STATE[args.workload] * B / (t_ms * 1e-3) / 1e12
+            kern = {"name": "tower_kernel (conv_body + res_body, tcgen05)" if args.workload == "conv_only"
+                    else "tower_tf_kernel (conv_body + res_body + transformer_body, tcgen05)", "ms": t_ms, "fc_ms": sum(fc_ms) / len(fc_ms),
                     "share_of_step": t_ms / step_ms_avg}
         line = {
             "metric": METRIC, "value": B * world * args.steps / (total_ms_max * 1e-3), "unit": UNIT, "n_gpus": world,
@@ -294,7 +297,7 @@ def run_ours(args):
                     "api": "at_engine_evaluate_host (pinned host buffers)"},
             "gpu_launches": int(launches_per_step * args.steps),
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                         "traffic": TOWER_DRAM_BYTES_PER_LAUNCH.get(B) if kern else None, "kernel": (kern or {}).get("name", "whole step (all kernels of the path)"),
+                         "traffic": TOWER_DRAM_BYTES_PER_LAUNCH.get(B) if (kern and args.workload == "conv_only") else None, "kernel": (kern or {}).get("name", "whole step (all kernels of the path)"),
                          "kernel_ms": (kern or {}).get("ms"), "fc_kernel_ms": (kern or {}).get("fc_ms"),
                          "kernel_share_of_step": (kern or {}).get("share_of_step"),
                          "peak_source": f"{peaks['source']} bf16 dense, {'sustained' if peak == peaks['sustained'] else 'burst'}",

@@ -193,6 +193,12 @@ int at_probe_umma(const void* d_a_image, int64_t a_bytes, const void* d_b_image,
                   uint32_t a_start_off, uint32_t a_lbo, uint32_t a_sbo, uint32_t a_kstep, uint32_t b_start_off, uint32_t b_lbo,
                   uint32_t b_sbo, uint32_t b_kstep, int layout_type, float* d_out /* [128,n] */, uint32_t* d_status, void* stream);
 
+/* Same chain with the A operand in tensor memory (rows = TMEM lanes, two bf16 per 32-bit column, written with
+ * tcgen05.st from row-major bf16 bit patterns [128,k]). Test-only: pins the layout the attention P*V product uses. */
+int at_probe_umma_ts(const void* d_a_rows, const void* d_b_image, int64_t b_bytes, int n, int k, int pack_mode, uint32_t a_col,
+                     uint32_t a_cols_per_kstep, uint32_t b_start_off, uint32_t b_lbo, uint32_t b_sbo, uint32_t b_kstep, float* d_out,
+                     uint32_t* d_status, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

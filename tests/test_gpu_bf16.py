@@ -22,14 +22,19 @@ def test_bf16_path_is_available_for_the_baseline_config():
     nn = network("conv_only", "bf16")
     assert nn.precision == _lib.PREC_BF16 and nn.engine.supports(_lib.PREC_BF16)
     assert network("conv_only", "auto").precision == _lib.PREC_BF16
+    assert network("default_tf", "auto").precision == _lib.PREC_BF16  # the reference's default model, transformer included
     # configurations outside the specialisation report why and stay on the fp32 path
     odd = network("odd_gelu", "auto")
     assert odd.precision == _lib.PREC_FP32 and not odd.engine.supports(_lib.PREC_BF16)
 
 
-def test_trunk_activation_matches_oracle(golden_dir):
-    mc, env, _seed, g = load_case("conv_only", golden_dir)
-    nn = network("conv_only", "bf16")
+BF16_CASES = ["conv_only", "default_tf"]  # BASELINE configs 2 and 3: conv tower alone / fused with the encoder layers
+
+
+@pytest.mark.parametrize("case", BF16_CASES)
+def test_trunk_activation_matches_oracle(case, golden_dir):
+    mc, env, _seed, g = load_case(case, golden_dir)
+    nn = network(case, "bf16")
     taps = []
     model_ref.forward(nn.get_weights(), mc, torch.from_numpy(g["grid"]), torch.from_numpy(g["other"]), taps)
     ref = taps[0].numpy()
@@ -38,9 +43,10 @@ def test_trunk_activation_matches_oracle(golden_dir):
     assert np.abs(got - ref).max() <= TRUNK_TOL * scale, (np.abs(got - ref).max(), scale)
 
 
-def test_bf16_matches_reference_golden(golden_dir):
-    mc, env, _seed, g = load_case("conv_only", golden_dir)
-    nn = network("conv_only", "bf16")
+@pytest.mark.parametrize("case", BF16_CASES)
+def test_bf16_matches_reference_golden(case, golden_dir):
+    mc, env, _seed, g = load_case(case, golden_dir)
+    nn = network(case, "bf16")
     probs, value = nn.evaluate_packed(torch.from_numpy(g["packed"]).cuda())
     probs, value = probs.cpu().numpy(), value.cpu().numpy()
     assert kl_rows(g["probs"], probs).max() <= KL_TOL
@@ -48,11 +54,12 @@ def test_bf16_matches_reference_golden(golden_dir):
     assert np.abs(probs.sum(axis=1) - 1.0).max() < 1e-5
 
 
+@pytest.mark.parametrize("case", BF16_CASES)
 @pytest.mark.parametrize("batch", [1, 2, 3, 127, 129, 1000])
-def test_bf16_ragged_batches_match_oracle(batch, golden_dir):
+def test_bf16_ragged_batches_match_oracle(case, batch, golden_dir):
     """Odd board counts (a half-empty pair), partial 128-board FC tiles, single states."""
-    mc, env, _seed, _g = load_case("conv_only", golden_dir)
-    nn = network("conv_only", "bf16")
+    mc, env, _seed, _g = load_case(case, golden_dir)
+    nn = network(case, "bf16")
     states = (synth_states(batch, env, seed=9000 + batch) + edge_states(env))[:batch]
     grid, other = features_ref.extract_batch(states, mc)
     torch.set_num_threads(8)
@@ -62,11 +69,12 @@ def test_bf16_ragged_batches_match_oracle(batch, golden_dir):
     assert np.abs(value.cpu().numpy() - v_ref).max() <= VALUE_TOL
 
 
-def test_bf16_full_batch_rows_are_independent(golden_dir):
+@pytest.mark.parametrize("case", BF16_CASES)
+def test_bf16_full_batch_rows_are_independent(case, golden_dir):
     """At the BASELINE batch (4096): every board's result equals the result of the same board in a small
     batch -- no cross-board leakage through the shared-memory images, TMEM or the FC tiles."""
-    mc, env, _seed, g = load_case("conv_only", golden_dir)
-    nn = network("conv_only", "bf16")
+    mc, env, _seed, g = load_case(case, golden_dir)
+    nn = network(case, "bf16")
     base = g["packed"]
     packed = np.tile(base, (-(-4096 // base.shape[0]), 1))[:4096]
     probs, value = nn.evaluate_packed(torch.from_numpy(packed).cuda())
