@@ -496,6 +496,11 @@ __global__ void gather_bias_kernel(const float* __restrict__ folded, const int64
 
 #include "at_bf16_tf.inc"
 
+constexpr size_t tower_tf_smem_bytes() {
+  return (size_t)kTfStages * kStageBytes + (size_t)kBoards * 2 * kBufBytes + (size_t)kMaxLayers * 128 * 4 + 9 * 128 * 4 + 128 * 4 +
+         (size_t)kXchFloats * 4 + (2 * kStages + 2) * 8 + 16;
+}
+
 }  // namespace
 
 // ---- host side ---------------------------------------------------------------------------------
@@ -699,8 +704,8 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
     }
     if (b->tf)
       for (int i = 0; i < 2; ++i) AT_CUDA_TRY(cudaMalloc(&b->tfp[i], (size_t)b->tfp_floats * sizeof(float)));
-    AT_CUDA_TRY(cudaFuncSetAttribute(tower_tf_kernel<AT_ACT_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
-    AT_CUDA_TRY(cudaFuncSetAttribute(tower_tf_kernel<AT_ACT_GELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+    AT_CUDA_TRY(cudaFuncSetAttribute(tower_tf_kernel<AT_ACT_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_tf_smem_bytes()));
+    AT_CUDA_TRY(cudaFuncSetAttribute(tower_tf_kernel<AT_ACT_GELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_tf_smem_bytes()));
     AT_CUDA_TRY(cudaMalloc(&b->d_bias_off, kMaxLayers * sizeof(int64_t)));
     AT_CUDA_TRY(cudaMalloc(&b->d_bias_w, kMaxLayers * sizeof(int)));
     AT_CUDA_TRY(cudaMemcpy(b->d_bias_off, b->bias_off.data(), b->bias_off.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
@@ -829,8 +834,8 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
     t.conv = tp;
     t.tfp = b->tfp[slot];
     t.pe = folded + p.pe;
-    if (tp.act0 == AT_ACT_RELU) tower_tf_kernel<AT_ACT_RELU><<<grid, kTfThreads, tower_smem_bytes(), st>>>(t);
-    else tower_tf_kernel<AT_ACT_GELU><<<grid, kTfThreads, tower_smem_bytes(), st>>>(t);
+    if (tp.act0 == AT_ACT_RELU) tower_tf_kernel<AT_ACT_RELU><<<grid, kTfThreads, tower_tf_smem_bytes(), st>>>(t);
+    else tower_tf_kernel<AT_ACT_GELU><<<grid, kTfThreads, tower_tf_smem_bytes(), st>>>(t);
   } else
   switch (tp.act0) {
     case AT_ACT_RELU: tower_kernel<AT_ACT_RELU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
