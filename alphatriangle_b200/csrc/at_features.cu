@@ -8,8 +8,8 @@
 // contraction) and one __double2float_rn per feature. Result: bit-exact.
 //
 // HBM-bound: 80 B in + (Cg*R*C + D)*4 B out per state (680 B at the defaults).
-// One block = 16 states; 16 lanes cooperate on a state's columns, then the whole
-// block streams the 16 states' outputs with fully coalesced stores.
+// One block = 16 states; the 16 lanes of a state share its columns (heights, holes),
+// then its 30 float64 feature divisions, then its output rows (float4 stores).
 
 #include "at_common.cuh"
 
@@ -37,7 +37,7 @@ __device__ __forceinline__ float store_f32(double v) {
 }
 
 __global__ void __launch_bounds__(kThreads) features_kernel(const PackedState* __restrict__ states, int64_t batch, int rows, int cols,
-                                                           int slots, int grid_channels, int other_dim,
+                                                           int slots, int grid_channels, int other_dim, int grid_vec4,
                                                            float* __restrict__ grid, float* __restrict__ other) {
   __shared__ PackedState s_state[kStatesPerBlock];
   __shared__ int s_height[kStatesPerBlock][AT_MAX_CELLS];
@@ -94,49 +94,55 @@ __global__ void __launch_bounds__(kThreads) features_kernel(const PackedState* _
       holes += __shfl_xor_sync(group_mask, holes, off, kLanesPerState);
       bump += __shfl_xor_sync(group_mask, bump, off, kLanesPerState);
     }
+    int dead = 0;
+    for (int w = 0; w < 4; ++w) {
+      const int lo = w * 32;
+      const uint32_t valid = cells >= lo + 32 ? 0xFFFFFFFFu : (cells > lo ? ((1u << (cells - lo)) - 1u) : 0u);
+      dead += __popc(st.death[w] & valid);
+    }
+    const int playable = cells - dead;
+    const double drows = (double)rows, dcols = (double)cols;
 
-    if (lane == 0) {
-      // _get_explicit_features (extractor.py:92-118)
-      int dead = 0;
-      for (int w = 0; w < 4; ++w) {
-        const int lo = w * 32;
-        uint32_t valid = cells >= lo + 32 ? 0xFFFFFFFFu : (cells > lo ? ((1u << (cells - lo)) - 1u) : 0u);
-        dead += __popc(st.death[w] & valid);
-      }
-      const int playable = cells - dead;
-      float* f = &s_other[s][slots * 8];
-      const double drows = (double)rows;
-      f[0] = store_f32(clip_d(__ddiv_rn(st.score, 100.0), -5.0, 5.0));
-      f[1] = store_f32(__ddiv_rn(__ddiv_rn((double)sum_h, (double)cols), drows));  // np.mean(heights) / rows
-      f[2] = store_f32(__ddiv_rn((double)max_h, drows));
-      f[3] = playable > 0 ? store_f32(__ddiv_rn((double)holes, (double)playable)) : 0.0f;
-      f[4] = cols > 1 ? store_f32(__ddiv_rn(__ddiv_rn((double)bump, (double)(cols - 1)), drows)) : 0.0f;
-      f[5] = store_f32(clip_d(__ddiv_rn((double)st.step, 1000.0), 0.0, 1.0));
-    } else if (lane <= slots) {
-      // _get_shape_features / _get_shape_availability (extractor.py:48-90), one lane per slot
-      const int i = lane - 1;
-      const int8_t* sl = st.slot[i];
-      const int present = sl[0] != 0;
-      const int n = (int)(uint8_t)sl[1];
-      float* f = &s_other[s][i * 7];
-      if (present && n > 0) {
-        const int ups = (int)(uint8_t)sl[2];
-        const int min_r = sl[4], min_c = sl[5], max_r = sl[6], max_c = sl[7];
-        const double dn = (double)n;
-        const double drows = (double)rows, dcols = (double)cols;
-        const double width_eff = __dadd_rn(__dmul_rn((double)(max_c - min_c + 1), 0.75), 0.25);
-        f[0] = store_f32(clip_d(__ddiv_rn(dn, 5.0), 0.0, 1.0));
-        f[1] = store_f32(__ddiv_rn((double)ups, dn));
-        f[2] = store_f32(__ddiv_rn((double)(n - ups), dn));
-        f[3] = store_f32(clip_d(__ddiv_rn((double)(max_r - min_r + 1), drows), 0.0, 1.0));
-        f[4] = store_f32(clip_d(__ddiv_rn(width_eff, dcols), 0.0, 1.0));
-        f[5] = store_f32(clip_d(__ddiv_rn(__ddiv_rn((double)(min_r + max_r), 2.0), drows), 0.0, 1.0));
-        f[6] = store_f32(clip_d(__ddiv_rn(__ddiv_rn((double)(min_c + max_c), 2.0), dcols), 0.0, 1.0));
+    // Every feature of the vector has the form clip((a / b) / c, lo, hi) in float64, rounded once to float32
+    // (extractor.py:48-118; dividing by 1.0 is exact, and the unclipped ratios lie in [0, 1] by construction), so the
+    // 16 lanes of a state share them out: lane l computes features l, l + 16, ...
+    for (int d = lane; d < n_full; d += kLanesPerState) {
+      double a = 0.0, b = 1.0, c = 1.0, lo = 0.0, hi = 1.0;
+      if (d < slots * 7) {
+        // _get_shape_features (extractor.py:48-85)
+        const int i = d / 7, k = d - i * 7;
+        const int8_t* sl = st.slot[i];
+        const int n = (int)(uint8_t)sl[1];
+        if (sl[0] != 0 && n > 0) {
+          const int ups = (int)(uint8_t)sl[2];
+          const int min_r = sl[4], min_c = sl[5], max_r = sl[6], max_c = sl[7];
+          switch (k) {
+            case 0: a = (double)n; b = 5.0; break;
+            case 1: a = (double)ups; b = (double)n; break;
+            case 2: a = (double)(n - ups); b = (double)n; break;
+            case 3: a = (double)(max_r - min_r + 1); b = drows; break;
+            case 4: a = __dadd_rn(__dmul_rn((double)(max_c - min_c + 1), 0.75), 0.25); b = dcols; break;
+            case 5: a = (double)(min_r + max_r); b = 2.0; c = drows; break;
+            default: a = (double)(min_c + max_c); b = 2.0; c = dcols; break;
+          }
+          if (k == 1 || k == 2) { lo = -1.0e300; hi = 1.0e300; }  // the reference does not clip these two
+        }
+      } else if (d < slots * 8) {
+        // _get_shape_availability (extractor.py:87-90)
+        a = st.slot[d - slots * 7][0] != 0 ? 1.0 : 0.0;
       } else {
-#pragma unroll
-        for (int k = 0; k < 7; ++k) f[k] = 0.0f;
+        // _get_explicit_features (extractor.py:92-118)
+        lo = -1.0e300; hi = 1.0e300;
+        switch (d - slots * 8) {
+          case 0: a = st.score; b = 100.0; lo = -5.0; hi = 5.0; break;
+          case 1: a = (double)sum_h; b = dcols; c = drows; break;                    // np.mean(heights) / rows
+          case 2: a = (double)max_h; b = drows; break;
+          case 3: if (playable > 0) { a = (double)holes; b = (double)playable; } break;
+          case 4: if (cols > 1) { a = (double)bump; b = (double)(cols - 1); c = drows; } break;
+          default: a = (double)st.step; b = 1000.0; lo = 0.0; hi = 1.0; break;
+        }
       }
-      s_other[s][slots * 7 + i] = present ? 1.0f : 0.0f;
+      s_other[s][d] = store_f32(clip_d(__ddiv_rn(__ddiv_rn(a, b), c), lo, hi));
     }
   }
   __syncthreads();
@@ -144,25 +150,27 @@ __global__ void __launch_bounds__(kThreads) features_kernel(const PackedState* _
   // other: concat [shape(7*slots), avail(slots), explicit(6)], zero-pad or truncate to D (extractor.py:120-139)
   {
     float* dst = other + first * other_dim;
-    const int total = n_here * other_dim;
-    for (int i = tid; i < total; i += kThreads) {
-      const int ss = i / other_dim, d = i - ss * other_dim;
-      dst[i] = d < n_full ? s_other[ss][d] : 0.0f;
-    }
+    if (s < n_here)
+      for (int d = lane; d < other_dim; d += kLanesPerState) dst[s * other_dim + d] = d < n_full ? s_other[s][d] : 0.0f;
   }
   // grid: channel 0 = +1 occupied&~death, -1 death, 0 otherwise; further channels zero (extractor.py:33-46)
-  {
+  if (s < n_here) {
+    const PackedState& st = s_state[s];
     const int per = grid_channels * cells;
-    float* dst = grid + first * per;
-    const int total = n_here * per;
-    for (int i = tid; i < total; i += kThreads) {
-      const int ss = i / per, e = i - ss * per;
-      float v = 0.0f;
-      if (e < cells) {
-        const PackedState& st = s_state[ss];
-        v = bit_at(st.death, e) ? -1.0f : (bit_at(st.occ, e) ? 1.0f : 0.0f);
+    float* dst = grid + (first + s) * per;
+    if (grid_vec4) {
+      for (int v4 = lane; v4 * 4 < per; v4 += kLanesPerState) {
+        float q[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const int e = v4 * 4 + j;
+          q[j] = e < cells ? (bit_at(st.death, e) ? -1.0f : (bit_at(st.occ, e) ? 1.0f : 0.0f)) : 0.0f;
+        }
+        *reinterpret_cast<float4*>(dst + v4 * 4) = make_float4(q[0], q[1], q[2], q[3]);
       }
-      dst[i] = v;
+    } else {
+      for (int e = lane; e < per; e += kLanesPerState)
+        dst[e] = e < cells ? (bit_at(st.death, e) ? -1.0f : (bit_at(st.occ, e) ? 1.0f : 0.0f)) : 0.0f;
     }
   }
 }
@@ -182,8 +190,9 @@ int launch_features(const at_env_desc& env, int grid_channels, int other_dim, co
   const int64_t blocks = (batch + kStatesPerBlock - 1) / kStatesPerBlock;
   if (blocks > 0x7FFFFFFF) return fail(AT_E_INVALID, "at_extract_features: batch too large");
   // slot layout inside s_other: shape features at [i*7], availability at [slots*7+i], explicit at [slots*8]
+  const int grid_vec4 = ((grid_channels * env.rows * env.cols) % 4 == 0) && ((reinterpret_cast<uintptr_t>(d_grid) & 15u) == 0);
   features_kernel<<<(unsigned)blocks, kThreads, 0, stream>>>(static_cast<const PackedState*>(d_states), batch, env.rows, env.cols,
-                                                              env.slots, grid_channels, other_dim, d_grid, d_other);
+                                                              env.slots, grid_channels, other_dim, grid_vec4, d_grid, d_other);
   AT_CUDA_TRY(cudaGetLastError());
   return AT_OK;
 }

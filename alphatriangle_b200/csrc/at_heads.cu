@@ -20,115 +20,105 @@ namespace {
 constexpr int TB = 32;         // boards per block
 constexpr int kThreads = 256;  // 8 warps: warp w owns boards 4w..4w+3 in the GEMM phases
 
-constexpr int KC = 16;        // weight rows staged per chunk
-constexpr int MAXP = 3;       // 128-wide output passes per thread (N <= 384)
-constexpr int MAXV = (KC * MAXP * 128 / 4 + kThreads - 1) / kThreads;  // float4 prefetch registers per thread
+// ReLU / identity inline, everything else (erf, tanh, exp based) behind one out-of-line call: this kernel applies the
+// activation in several unrolled places and has to stay small enough for the instruction cache.
+__device__ __noinline__ float act_slow(float x, int act) { return apply_act(x, act); }
+__device__ __forceinline__ float act_small(float x, int act) {
+  return act == AT_ACT_RELU ? fmaxf(x, 0.0f) : (act == AT_ACT_NONE ? x : act_slow(x, act));
+}
 
-// C_s[b][n] = act(bias[n] + sum_k A_s[b][k] * Wt[k][n]) for b < TB, n < N.
-// Weights go global -> registers -> shared in chunks of KC rows, double-buffered so the next chunk's loads are in
-// flight while the current one is consumed. Warp w computes boards 4w..4w+3 (their A rows are warp-wide broadcast
-// float4 loads), lane l the outputs 4l..4l+3 of each 128-wide pass. Needs K % 4 == 0 and lda % 4 == 0.
+constexpr int KC = 16;   // weight rows staged per chunk
+constexpr int PW = 128;  // output columns per pass (32 lanes x float4)
+
+// C_s[b][n] = act(bias[n] + sum_k A_s[b][k] * Wt[k][n]) for b < TB, n < N, in passes of 128 output columns.
+// Weights go global -> registers -> shared in chunks of KC rows x 128 columns, double-buffered so the next chunk's
+// loads are in flight while the current one is consumed. Warp w computes boards 4w..4w+3 (their A rows are warp-wide
+// broadcast float4 loads), lane l the outputs 4l..4l+3 of the pass. Needs K % 4 == 0 and lda % 4 == 0. Kept out of
+// line and free of big unrolls on purpose: the kernel calls it four times and must stay inside the instruction cache.
 __device__ __noinline__ void block_gemm(const float* __restrict__ A_s, int lda, int K, const float* __restrict__ Wt,
-                                           const float* __restrict__ bias, int N, float* __restrict__ C_s, int ldc, int act,
-                                           float* __restrict__ Ws) {
+                                        const float* __restrict__ bias, int N, float* __restrict__ C_s, int ldc, int act,
+                                        float* __restrict__ Ws) {
   const int tid = threadIdx.x, warp = tid / 32, lane = tid % 32;
-  const int n_pad = (N + 3) & ~3, n4 = n_pad / 4;
   const bool vec = (N & 3) == 0;
-  const int chunk_v = KC * n4;  // float4 per chunk
   const int n_chunks = (K + KC - 1) / KC;
-  float4 pre[MAXV];
+  const int ld_k = tid / 32, ld_c = tid % 32;  // this thread stages rows ld_k and ld_k + 8, float4 column ld_c of every chunk
+  const float* a_rows = A_s + (warp * 4) * lda;
+  float4* Ws4 = reinterpret_cast<float4*>(Ws);
 
-  auto fetch = [&](int c) {
+  for (int n_base = 0; n_base < N; n_base += PW) {
+    const int n0 = n_base + lane * 4;       // this lane's four output columns
+    const int ln = n_base + ld_c * 4;       // the four columns this thread stages
+    float4 pre[2];
+    auto fetch = [&](int c) {
 #pragma unroll
-    for (int r = 0; r < MAXV; ++r) {
-      const int i = tid + r * kThreads;
-      float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (i < chunk_v) {
-        const int kk = i / n4, c4 = i - kk * n4;
-        const int k = c * KC + kk;
-        if (k < K) {
-          const float* src = Wt + (size_t)k * N + c4 * 4;
+      for (int r = 0; r < 2; ++r) {
+        const int k = c * KC + ld_k + r * 8;
+        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (k < K && ln < N) {
+          const float* src = Wt + (size_t)k * N + ln;
           if (vec) {
             v = __ldg(reinterpret_cast<const float4*>(src));
           } else {
-            const int n = c4 * 4;
-            v.x = n < N ? __ldg(src) : 0.f;
-            v.y = n + 1 < N ? __ldg(src + 1) : 0.f;
-            v.z = n + 2 < N ? __ldg(src + 2) : 0.f;
-            v.w = n + 3 < N ? __ldg(src + 3) : 0.f;
+            v.x = __ldg(src);
+            v.y = ln + 1 < N ? __ldg(src + 1) : 0.f;
+            v.z = ln + 2 < N ? __ldg(src + 2) : 0.f;
+            v.w = ln + 3 < N ? __ldg(src + 3) : 0.f;
           }
         }
+        pre[r] = v;
       }
-      pre[r] = v;
-    }
-  };
-  auto stash = [&](int buf) {
-    float4* dst = reinterpret_cast<float4*>(Ws) + (size_t)buf * KC * MAXP * 32;
-#pragma unroll
-    for (int r = 0; r < MAXV; ++r) {
-      const int i = tid + r * kThreads;
-      if (i < chunk_v) dst[i] = pre[r];
-    }
-  };
-
-  float acc[MAXP][4][4];
-#pragma unroll
-  for (int ps = 0; ps < MAXP; ++ps)
+    };
+    auto stash = [&](int buf) {
+      Ws4[(buf * KC + ld_k) * 32 + ld_c] = pre[0];
+      Ws4[(buf * KC + ld_k + 8) * 32 + ld_c] = pre[1];
+    };
+    float acc[4][4];
 #pragma unroll
     for (int i = 0; i < 4; ++i)
 #pragma unroll
-      for (int j = 0; j < 4; ++j) acc[ps][i][j] = 0.0f;
+      for (int j = 0; j < 4; ++j) acc[i][j] = 0.0f;
 
-  fetch(0);
-  __syncthreads();  // every warp is done with whatever used Ws before
-  stash(0);
-  __syncthreads();
-  const float* a_rows = A_s + (warp * 4) * lda;
-  for (int c = 0; c < n_chunks; ++c) {
-    if (c + 1 < n_chunks) fetch(c + 1);
-    const float4* W4 = reinterpret_cast<const float4*>(Ws) + (size_t)(c & 1) * KC * MAXP * 32;
-    const int k_here = min(KC, K - c * KC);
-    for (int kk = 0; kk < k_here; kk += 4) {
-      float4 a[4];
+    fetch(0);
+    __syncthreads();  // every warp is done with whatever used Ws before
+    stash(0);
+    __syncthreads();
+    for (int c = 0; c < n_chunks; ++c) {
+      if (c + 1 < n_chunks) fetch(c + 1);
+      const float4* W4 = Ws4 + (c & 1) * KC * 32 + lane;
+      const int k_here = min(KC, K - c * KC);
+#pragma unroll 1
+      for (int kk = 0; kk < k_here; kk += 4) {
+        float4 a[4];
 #pragma unroll
-      for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(a_rows + i * lda + c * KC + kk);
+        for (int i = 0; i < 4; ++i) a[i] = *reinterpret_cast<const float4*>(a_rows + i * lda + c * KC + kk);
 #pragma unroll
-      for (int ps = 0; ps < MAXP; ++ps) {
-        const int g = ps * 32 + lane;  // float4 column group
-        if (g < n4) {
+        for (int j4 = 0; j4 < 4; ++j4) {
+          const float4 w = W4[(kk + j4) * 32];
 #pragma unroll
-          for (int j4 = 0; j4 < 4; ++j4) {
-            const float4 w = W4[(kk + j4) * n4 + g];
-#pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const float av = j4 == 0 ? a[i].x : (j4 == 1 ? a[i].y : (j4 == 2 ? a[i].z : a[i].w));
-              acc[ps][i][0] = fmaf(av, w.x, acc[ps][i][0]);
-              acc[ps][i][1] = fmaf(av, w.y, acc[ps][i][1]);
-              acc[ps][i][2] = fmaf(av, w.z, acc[ps][i][2]);
-              acc[ps][i][3] = fmaf(av, w.w, acc[ps][i][3]);
-            }
+          for (int i = 0; i < 4; ++i) {
+            const float av = j4 == 0 ? a[i].x : (j4 == 1 ? a[i].y : (j4 == 2 ? a[i].z : a[i].w));
+            acc[i][0] = fmaf(av, w.x, acc[i][0]);
+            acc[i][1] = fmaf(av, w.y, acc[i][1]);
+            acc[i][2] = fmaf(av, w.z, acc[i][2]);
+            acc[i][3] = fmaf(av, w.w, acc[i][3]);
           }
         }
       }
+      if (c + 1 < n_chunks) stash((c + 1) & 1);
+      __syncthreads();
     }
-    if (c + 1 < n_chunks) stash((c + 1) & 1);
-    __syncthreads();
-  }
-#pragma unroll
-  for (int ps = 0; ps < MAXP; ++ps) {
-    const int n0 = (ps * 32 + lane) * 4;
 #pragma unroll
     for (int j = 0; j < 4; ++j) {
       if (n0 + j < N) {
         const float bv = bias[n0 + j];
 #pragma unroll
-        for (int i = 0; i < 4; ++i) C_s[(warp * 4 + i) * ldc + n0 + j] = apply_act(acc[ps][i][j] + bv, act);
+        for (int i = 0; i < 4; ++i) C_s[(warp * 4 + i) * ldc + n0 + j] = act_small(acc[i][j] + bv, act);
       }
     }
   }
 }
 
-__global__ void __launch_bounds__(kThreads, 1) heads_fused_kernel(const HeadsParams p) {
+__global__ void __launch_bounds__(kThreads, 2) heads_fused_kernel(const HeadsParams p) {
   extern __shared__ __align__(16) float sm[];
   const int T = p.trunk_n, HP = p.pol_hidden, HV = p.val_hidden;
   float* t_s = sm;                    // [TB][T]
@@ -137,7 +127,7 @@ __global__ void __launch_bounds__(kThreads, 1) heads_fused_kernel(const HeadsPar
   float* pl_s = hv_s + TB * HV;       // [TB][actions]
   float* vl_s = pl_s + TB * p.actions;  // [TB][atoms]
   float* o_s = vl_s + TB * p.atoms;   // [TB][other_dim]
-  float* w_s = sm + p.w_stage_off;    // [2][KC][MAXP*128] weight staging (16-byte aligned)
+  float* w_s = sm + p.w_stage_off;    // [2][KC][128] weight staging (16-byte aligned)
 
   const int tid = threadIdx.x, warp = tid / 32, lane = tid % 32;
   const int64_t b0 = (int64_t)blockIdx.x * TB;
@@ -158,7 +148,7 @@ __global__ void __launch_bounds__(kThreads, 1) heads_fused_kernel(const HeadsPar
       const float* wo = p.w_other + n;
       const float* ob = o_s + b * p.other_dim;
       for (int k = 0; k < p.other_dim; ++k) v = fmaf(ob[k], wo[(size_t)k * T], v);
-      v = apply_act(v, p.act);
+      v = act_small(v, p.act);
     }
     t_s[i] = v;
   }
@@ -239,12 +229,11 @@ static size_t act_floats(const HeadsParams& p) {
   return (n + 3) & ~size_t(3);
 }
 
-size_t heads_fused_smem(const HeadsParams& p) { return (act_floats(p) + (size_t)2 * KC * MAXP * 128) * sizeof(float); }
+size_t heads_fused_smem(const HeadsParams& p) { return (act_floats(p) + (size_t)2 * KC * PW) * sizeof(float); }
 
 bool heads_fused_supported(const HeadsParams& p) {
   const bool dims4 = (p.trunk_n % 4 == 0) && (p.pol_hidden % 4 == 0) && (p.val_hidden % 4 == 0);
-  const bool fits = p.pol_hidden <= MAXP * 128 && p.val_hidden <= MAXP * 128 && p.actions <= MAXP * 128 && p.atoms <= MAXP * 128;
-  return p.trunk_n > 0 && dims4 && fits && heads_fused_smem(p) <= 200 * 1024;
+  return p.trunk_n > 0 && dims4 && heads_fused_smem(p) <= 200 * 1024;
 }
 
 int launch_heads_fused(const HeadsParams& p, cudaStream_t stream, int64_t* launches) {
