@@ -50,7 +50,12 @@ constexpr int kMaxSlabs = 36;                // weight slabs per layer (9 taps x
 constexpr int kBoards = 2;                   // boards in flight per CTA
 constexpr int kEpiSplit = 2;                 // epilogue warps per (board, TMEM lane quarter): each takes 1/kEpiSplit of the channels
 constexpr int kEpiWarps = kBoards * 4 * kEpiSplit;
-constexpr int kTowerThreads = 64 + kEpiWarps * 32;
+constexpr int kMmaWarpB = 2 + kEpiWarps;      // second MMA-issuing warp (odd slabs); warp 1 takes the even ones
+constexpr int kTowerThreads = 64 + kEpiWarps * 32 + 32;
+constexpr int kMaxBars = 32;                 // mbarrier slots reserved in shared memory
+// CTA-pair mode (cta_group::2): each CTA streams half of every weight slab, so stages are half as big and twice as many
+constexpr int kStages2 = 8;
+constexpr int kStageBytes2 = 8192;
 constexpr long long kTimeoutCycles = 2000000000LL;  // ~1 s: a wedged pipeline reports instead of hanging
 
 struct TowerLayer {
@@ -83,7 +88,7 @@ struct TowerParams {
 
 constexpr size_t tower_smem_bytes() {
   return (size_t)kStages * kStageBytes + (size_t)kBoards * 2 * kBufBytes + (size_t)kMaxLayers * 128 * 4 + 9 * 128 * 4 + 128 * 4 +
-         (2 * kStages + 2) * 8 + 16;
+         kMaxBars * 8 + 16;
 }
 
 __device__ __forceinline__ bool elect_one() {
@@ -96,6 +101,19 @@ __device__ __forceinline__ bool wait_bar(uint32_t bar, uint32_t parity, uint32_t
   if (mbar_try_wait(bar, parity)) return true;  // common case: no clock reads on the fast path
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > kTimeoutCycles) {
+      atomicOr(status, code);
+      return false;
+    }
+  }
+  return true;
+}
+
+// same, for a barrier the peer CTA of the pair arrives on (cluster-scope acquire)
+__device__ __forceinline__ bool wait_bar_cluster(uint32_t bar, uint32_t parity, uint32_t* status, uint32_t code) {
+  if (mbar_try_wait_cluster(bar, parity)) return true;
+  const long long t0 = clock64();
+  while (!mbar_try_wait_cluster(bar, parity)) {
     if (clock64() - t0 > kTimeoutCycles) {
       atomicOr(status, code);
       return false;
@@ -127,7 +145,7 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
 
 // One weight slab against both boards' images: NM K-steps of 16 channels each, A advancing two 8-channel planes per
 // step, B advancing two planes of the slab. Descriptor high words are constant (SBO = 128 B, version 1, no swizzle).
-template <int NM>
+template <int NM, bool PAIR = false>
 __device__ __forceinline__ void issue_slab(uint32_t tmem_base, uint32_t a0_16, uint32_t a1_16, uint32_t b16, uint32_t a_lo_fixed,
                                            uint32_t b_lo_fixed, uint32_t b_step16, uint32_t idesc, bool first,
                                            uint32_t tmem_board_stride = 128) {
@@ -139,15 +157,28 @@ __device__ __forceinline__ void issue_slab(uint32_t tmem_base, uint32_t a0_16, u
     for (int j = 0; j < NM; ++j) {
       const uint32_t a_lo = a_lo_fixed | (a16 + (uint32_t)j * (2 * kPlaneBytes >> 4));
       const uint32_t b_lo = b_lo_fixed | (b16 + (uint32_t)j * b_step16);
-      mma_bf16(tmem_base + (uint32_t)b * tmem_board_stride, ((uint64_t)kDescHi << 32) | a_lo, ((uint64_t)kDescHi << 32) | b_lo, idesc,
-               !(first && j == 0));
+      if constexpr (PAIR)
+        mma_bf16_2cta(tmem_base + (uint32_t)b * tmem_board_stride, ((uint64_t)kDescHi << 32) | a_lo, ((uint64_t)kDescHi << 32) | b_lo, idesc,
+                      !(first && j == 0));
+      else
+        mma_bf16(tmem_base + (uint32_t)b * tmem_board_stride, ((uint64_t)kDescHi << 32) | a_lo, ((uint64_t)kDescHi << 32) | b_lo, idesc,
+                 !(first && j == 0));
     }
   }
 }
 
 // ACT = the model-wide activation (every conv_block and ResidualBlock of a model shares it, model.py:127)
-template <int ACT>
+// PAIR = two CTAs of a cluster drive one tensor-core pair (tcgen05 cta_group::2): every MMA covers board b of BOTH CTAs
+// (M = 256) and each CTA keeps only its half of the weight slab (N/2 rows of B), which halves the shared-memory reads
+// of B per SM and the L2 -> SM weight traffic. Rank 0 issues; rank 1's MMA warp only relays "my half has landed".
+// MODE 0: one CTA per SM, 4 ring stages of 16 KB (64 K-values per slab); MODE 1: CTA pairs, 8 stages of 8 KB (each CTA's half of
+// a 64-K slab); MODE 2: one CTA per SM, 8 stages of 8 KB (32 K-values per slab) -- twice as many slabs in flight.
+template <int ACT, int MODE>
 __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_constant__ TowerParams p) {
+  constexpr bool PAIR = MODE == 1;
+  constexpr int NS = MODE != 0 ? kStages2 : kStages;               // ring stages
+  constexpr uint32_t SB = MODE != 0 ? kStageBytes2 : kStageBytes;  // bytes per stage
+  static_assert(NS * SB == kStages * kStageBytes, "both modes use the same ring footprint");
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* ring = smem;
   uint8_t* act = ring + kStages * kStageBytes;                        // [board][buf][kBufBytes]
@@ -155,12 +186,17 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   float* s_w0 = s_bias + kMaxLayers * 128;                            // [9][c0]
   float* s_b0 = s_w0 + 9 * 128;                                       // [c0]
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_b0 + 128);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 2);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kMaxBars);
 
   const int tid = threadIdx.x, warp = tid / 32, lane = tid % 32;
+  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
   const uint32_t ring_u = smem_u32(ring), act_u = smem_u32(act);
-  const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + kStages);
-  const uint32_t bar_acc = smem_u32(bars + 2 * kStages), bar_act = smem_u32(bars + 2 * kStages + 1);
+  const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + NS), bar_full2 = smem_u32(bars + 2 * NS);
+  const uint32_t bar_acc = smem_u32(bars + 3 * NS), bar_act = smem_u32(bars + 3 * NS + 1), bar_first = smem_u32(bars + 3 * NS + 2);
+  // Two warps issue MMAs, taking alternate weight slabs: issuing a tcgen05.mma holds the issuing warp until the tensor pipe
+  // accepts it, so a single issuer cannot overlap its per-slab bookkeeping (barrier wait, descriptors, commit: ~400 cycles)
+  // with the 512 cycles its 8 MMAs run -- measured additive. With two issuers one warp's bookkeeping hides under the other's MMAs.
+  constexpr int kIssuers = PAIR ? 1 : 2;
 
   // ---- one-time setup --------------------------------------------------------------------
   for (int i = tid; i < kBoards * 2 * kBufBytes / 16; i += kTowerThreads) reinterpret_cast<uint4*>(act)[i] = make_uint4(0, 0, 0, 0);
@@ -168,25 +204,36 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   for (int i = tid; i < 9 * p.c0; i += kTowerThreads) s_w0[i] = p.w0[i];
   for (int i = tid; i < p.c0; i += kTowerThreads) s_b0[i] = p.b0[i];
   if (tid == 0) {
-    for (int i = 0; i < kStages; ++i) {
+    for (int i = 0; i < NS; ++i) {
       mbar_init(bar_full + 8 * i, 1);
       mbar_init(bar_empty + 8 * i, 1);
+      mbar_init(bar_full2 + 8 * i, 1);
     }
-    mbar_init(bar_acc, 1);
-    mbar_init(bar_act, kEpiWarps);  // one arrival per epilogue warp
+    mbar_init(bar_acc, kIssuers);                          // every issuing warp commits its share of the layer
+    mbar_init(bar_first, 1);
+    mbar_init(bar_act, PAIR ? 2 * kEpiWarps : kEpiWarps);  // one arrival per epilogue warp (of both CTAs in pair mode)
     fence_mbar_init();
   }
   if (warp == 0) {
-    tmem_alloc(smem_u32(tmem_slot), kBoards * 128);
-    tmem_relinquish();
+    if constexpr (PAIR) {
+      tmem_alloc2(smem_u32(tmem_slot), kBoards * 128);
+      tmem_relinquish2();
+    } else {
+      tmem_alloc(smem_u32(tmem_slot), kBoards * 128);
+      tmem_relinquish();
+    }
   }
   fence_proxy_async_smem();  // the zeroed halos are read by the tensor core (async proxy)
   tc_fence_before();
   __syncthreads();
+  if constexpr (PAIR) cluster_sync_all();  // the peer's barriers exist before anyone arrives on them remotely
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   const int64_t n_pairs = (p.batch + kBoards - 1) / kBoards;
+  // this CTA's first board pair; both CTAs of a cluster run the same number of rounds (the second may idle on the tail)
+  const int64_t pair0 = blockIdx.x;
+  const int64_t lead0 = PAIR ? (int64_t)(blockIdx.x & ~1u) : (int64_t)blockIdx.x;
 
   if (warp == 0) {
     // ===== weight producer: one lane streams every layer's slabs through the ring =====
@@ -194,10 +241,11 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
       int stage = 0;
       uint32_t phase = 0;
       bool ok = true;
-      for (int64_t pair = blockIdx.x; pair < n_pairs && ok; pair += gridDim.x) {
+      for (int64_t lead = lead0; lead < n_pairs && ok; lead += gridDim.x) {
         const uint8_t* src = p.wstream;
         for (int l = 0; l < p.n_layers && ok; ++l) {
-          const uint32_t bytes = p.layers[l].slab_bytes;
+          const uint32_t slab = p.layers[l].slab_bytes;
+          const uint32_t bytes = PAIR ? slab / 2 : slab;  // pair mode: this CTA's N/2 rows, stored as [slab][half]
           for (int s = 0; s < p.layers[l].n_slabs; ++s) {
             ok = wait_bar(bar_empty + 8 * stage, phase ^ 1, p.status, 1u);
             if (!ok) break;
@@ -205,56 +253,87 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
               mbar_arrive(bar_full + 8 * stage);
             } else {
               mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
-              bulk_g2s(ring_u + stage * kStageBytes, src, bytes, bar_full + 8 * stage);
+              bulk_g2s(ring_u + stage * SB, src + (PAIR ? rank * bytes : 0u), bytes, bar_full + 8 * stage);
             }
-            src += bytes;
-            if (++stage == kStages) { stage = 0; phase ^= 1; }
+            src += slab;
+            if (++stage == NS) { stage = 0; phase ^= 1; }
           }
         }
       }
     }
-  } else if (warp == 1) {
-    // ===== MMA issuer: the warp stays converged; one elected lane issues tcgen05.mma / commit =====
+  } else if (warp == 1 || warp == kMmaWarpB) {
+    // ===== MMA issuers: each warp stays converged; one elected lane issues tcgen05.mma / commit =====
+    const int me = warp == 1 ? 0 : 1;  // which of the alternating slabs this warp takes
     int stage = 0;
-    uint32_t phase = 0, act_phase = 0;
+    uint32_t phase = 0, act_phase = 0, first_phase = 0;
     bool ok = true;
     const uint32_t a_lo_fixed = (uint32_t)(kPlaneBytes >> 4) << 16;  // LBO = one 8-channel plane
-    for (int64_t pair = blockIdx.x; pair < n_pairs && ok; pair += gridDim.x) {
-      for (int l = 0; l < p.n_layers && ok; ++l) {
-        const TowerLayer& L = p.layers[l];
-        ok = __all_sync(0xffffffffu, wait_bar(bar_act, act_phase, p.status, 2u));  // this layer's input images are written
-        if (!ok) break;
-        act_phase ^= 1;
-        tc_fence_after();
-        const uint32_t idesc = idesc_bf16(kM, (uint32_t)L.cout);
-        const uint32_t b_lbo16 = (uint32_t)L.cout;  // bytes between 8-channel planes of a slab, >> 4
-        const uint32_t b_lo_fixed = b_lbo16 << 16;
-        const int mma_per_slab = L.ks / 16;
-        const int n_slabs = L.n_slabs;
-        const uint32_t a0_img16 = (act_u + (uint32_t)(0 * 2 + L.src) * kBufBytes) >> 4;
-        const uint32_t a1_img16 = (act_u + (uint32_t)(1 * 2 + L.src) * kBufBytes) >> 4;
-        for (int s = 0; s < n_slabs; ++s) {
-          const uint32_t a_off16 = L.aoff[s];
-          ok = __all_sync(0xffffffffu, wait_bar(bar_full + 8 * stage, phase, p.status, 4u));
+    if (PAIR && me != 0) {
+      // pair mode keeps a single issuer
+    } else if (PAIR && rank != 0) {
+      // rank 1 of a pair issues nothing: it tells the leader when its half of each slab has landed
+      for (int64_t lead = lead0; lead < n_pairs && ok; lead += gridDim.x)
+        for (int l = 0; l < p.n_layers && ok; ++l)
+          for (int s = 0; s < p.layers[l].n_slabs; ++s) {
+            ok = __all_sync(0xffffffffu, wait_bar(bar_full + 8 * stage, phase, p.status, 4u));
+            if (!ok) break;
+            if (lane == 0) mbar_arrive_remote(mapa_smem(bar_full2 + 8 * stage, 0));
+            __syncwarp();
+            if (++stage == NS) { stage = 0; phase ^= 1; }
+          }
+    } else {
+      for (int64_t lead = lead0; lead < n_pairs && ok; lead += gridDim.x) {
+        for (int l = 0; l < p.n_layers && ok; ++l) {
+          const TowerLayer& L = p.layers[l];
+          // this layer's input images are written (in pair mode: in both CTAs)
+          ok = __all_sync(0xffffffffu, PAIR ? wait_bar_cluster(bar_act, act_phase, p.status, 2u) : wait_bar(bar_act, act_phase, p.status, 2u));
           if (!ok) break;
+          act_phase ^= 1;
           tc_fence_after();
-          const uint32_t b16 = (ring_u + stage * kStageBytes) >> 4;
-          if (elect_one()) {
-            if (!(p.debug & 2u)) {
-              if (mma_per_slab == 4)
-                issue_slab<4>(tmem_base, a0_img16 + a_off16, a1_img16 + a_off16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
-              else if (mma_per_slab == 2)
-                issue_slab<2>(tmem_base, a0_img16 + a_off16, a1_img16 + a_off16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
-              else
-                issue_slab<1>(tmem_base, a0_img16 + a_off16, a1_img16 + a_off16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
+          const uint32_t idesc = idesc_bf16(PAIR ? 2 * kM : kM, (uint32_t)L.cout);
+          const uint32_t b_lbo16 = PAIR ? (uint32_t)L.cout / 2 : (uint32_t)L.cout;  // 8-channel plane of this CTA's B rows, >> 4
+          const uint32_t b_lo_fixed = b_lbo16 << 16;
+          const int mma_per_slab = L.ks / 16;
+          const int n_slabs = L.n_slabs;
+          const uint32_t a0_img16 = (act_u + (uint32_t)(0 * 2 + L.src) * kBufBytes) >> 4;
+          const uint32_t a1_img16 = (act_u + (uint32_t)(1 * 2 + L.src) * kBufBytes) >> 4;
+          for (int s = 0; s < n_slabs; ++s) {
+            if (kIssuers == 2 && (s & 1) != me) {  // the other warp's slab: just keep the ring position in step
+              if (++stage == NS) { stage = 0; phase ^= 1; }
+              continue;
             }
-            mma_commit(bar_empty + 8 * stage);  // slab may be overwritten once these MMAs retire
+            const uint32_t a_off16 = L.aoff[s];
+            ok = __all_sync(0xffffffffu, wait_bar(bar_full + 8 * stage, phase, p.status, 4u));
+            if (ok && PAIR) ok = __all_sync(0xffffffffu, wait_bar_cluster(bar_full2 + 8 * stage, phase, p.status, 32u));
+            // slab 0 carries the MMAs that overwrite (rather than accumulate into) the accumulators: nobody issues before it
+            if (ok && kIssuers == 2 && me == 1 && s == 1) ok = __all_sync(0xffffffffu, wait_bar(bar_first, first_phase, p.status, 64u));
+            if (!ok) break;
+            tc_fence_after();
+            const uint32_t b16 = (ring_u + stage * SB) >> 4;
+            if (elect_one()) {
+              if (!(p.debug & 2u)) {
+                if (mma_per_slab == 4)
+                  issue_slab<4, PAIR>(tmem_base, a0_img16 + a_off16, a1_img16 + a_off16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
+                else if (mma_per_slab == 2)
+                  issue_slab<2, PAIR>(tmem_base, a0_img16 + a_off16, a1_img16 + a_off16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
+                else
+                  issue_slab<1, PAIR>(tmem_base, a0_img16 + a_off16, a1_img16 + a_off16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
+              }
+              // the slab may be overwritten (in both CTAs) once these MMAs retire
+              if constexpr (PAIR) mma_commit_2cta(bar_empty + 8 * stage, 3);
+              else mma_commit(bar_empty + 8 * stage);
+              if (kIssuers == 2 && s == 0) mbar_arrive(bar_first);  // the overwriting MMAs are in the pipe
+            }
+            __syncwarp();
+            if (++stage == NS) { stage = 0; phase ^= 1; }
+          }
+          first_phase ^= 1;
+          if (ok && elect_one()) {  // every board's accumulator of this layer is complete
+            if constexpr (PAIR) mma_commit_2cta(bar_acc, 3);
+            else mma_commit(bar_acc);
           }
           __syncwarp();
-          if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
-        if (ok && elect_one()) mma_commit(bar_acc);  // both boards' accumulators are complete
-        __syncwarp();
       }
     }
   } else {
@@ -270,7 +349,17 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     const uint32_t tmem_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)eb * 128;
     uint32_t acc_phase = 0;
     bool ok = true;
-    for (int64_t pair = blockIdx.x; pair < n_pairs && ok; pair += gridDim.x) {
+    // "this layer's image is written": in pair mode every epilogue warp of both CTAs reports to the leader's barrier
+    const uint32_t act_target = PAIR && rank != 0 ? mapa_smem(bar_act, 0) : bar_act;
+    auto arrive_act = [&]() {
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        if (PAIR && rank != 0) mbar_arrive_remote(act_target);
+        else mbar_arrive(bar_act);
+      }
+    };
+    for (int64_t lead = lead0, pair = pair0; lead < n_pairs && ok; lead += gridDim.x, pair += gridDim.x) {
       const int64_t board = pair * kBoards + eb;
       const bool valid = board < p.batch;
       // ---- layer 0 on CUDA cores, straight from the bitmasks (extractor.py:33-46 + conv_body.0) ----
@@ -307,9 +396,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
                  make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7])));
         }
       }
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar_act);
+      arrive_act();
 
       for (int l = 0; l < p.n_layers; ++l) {
         const TowerLayer& L = p.layers[l];
@@ -350,18 +437,19 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
           }
         }
         tc_fence_before();  // TMEM reads are done before the next layer's MMAs overwrite the accumulator
-        if (l + 1 < p.n_layers) {
-          fence_proxy_async_smem();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(bar_act);
-        }
+        if (l + 1 < p.n_layers) arrive_act();
       }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem_base, kBoards * 128);
+  if constexpr (PAIR) {
+    cluster_sync_all();  // neither CTA frees tensor memory or exits while its peer may still touch it
+    if (warp == 0) tmem_dealloc2(tmem_base, kBoards * 128);
+  } else {
+    if (warp == 0) tmem_dealloc(tmem_base, kBoards * 128);
+  }
 }
 
 // ---- trunk FC: split-K tcgen05 GEMM ---------------------------------------------------------
@@ -487,6 +575,23 @@ __global__ void __launch_bounds__(256) pack_b_kernel(const float* __restrict__ w
   }
 }
 
+// same weights for CTA-pair mode: every slab of `ks` K-values is stored as two halves, [slab][half][ks/8][N/2][8], so that
+// each CTA of a pair bulk-copies just the N/2 rows of B it feeds to the shared MMA
+__global__ void __launch_bounds__(256) pack_b_split_kernel(const float* __restrict__ wt, int K, int N, int ks, __nv_bfloat16* __restrict__ dst) {
+  const int64_t total = (int64_t)K * N;
+  const int hn = N / 2;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int e = (int)(i % 8);
+    int64_t t = i / 8;
+    const int row = (int)(t % hn); t /= hn;
+    const int plane = (int)(t % (ks / 8)); t /= (ks / 8);
+    const int half = (int)(t % 2);
+    const int slab = (int)(t / 2);
+    const int k = slab * ks + plane * 8 + e, n = half * hn + row;
+    dst[i] = __float2bfloat16_rn(wt[(int64_t)k * N + n]);
+  }
+}
+
 __global__ void gather_bias_kernel(const float* __restrict__ folded, const int64_t* __restrict__ offs, const int* __restrict__ widths,
                                    int n_layers, float* __restrict__ dst) {
   const int l = blockIdx.x;
@@ -515,6 +620,9 @@ struct Bf16Path {
   size_t wstream_bytes = 0;
   // per weight set
   uint8_t* wstream[2] = {nullptr, nullptr};
+  uint8_t* wstream_pair[2] = {nullptr, nullptr};  // the same slabs split in halves for CTA-pair mode
+  std::vector<int> layer_ks;
+  bool pair_mode = false;
   uint8_t* wfc[2] = {nullptr, nullptr};
   float* bias[2] = {nullptr, nullptr};
   int64_t* d_bias_off = nullptr;
@@ -612,6 +720,7 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
     L.src = src; L.dst = dst; L.res = res; L.act = c.f.act; L.bias_slot = slot;
     b->layer_wt.push_back(c.f.wt);
     b->layer_k.push_back(c.f.K);
+    b->layer_ks.push_back(L.ks);
     b->bias_off.push_back(c.f.bias);
     b->bias_w.push_back(c.cout);
     b->wstream_bytes += (size_t)c.f.K * c.cout * 2;
@@ -699,6 +808,7 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
   auto alloc = [&]() -> int {
     for (int i = 0; i < 2; ++i) {
       AT_CUDA_TRY(cudaMalloc(&b->wstream[i], b->wstream_bytes));
+      if (!b->tf) AT_CUDA_TRY(cudaMalloc(&b->wstream_pair[i], b->conv_stream_bytes));
       AT_CUDA_TRY(cudaMalloc(&b->wfc[i], (size_t)p.flat * fc.N * 2));
       AT_CUDA_TRY(cudaMalloc(&b->bias[i], (size_t)kMaxLayers * 128 * sizeof(float)));
     }
@@ -718,11 +828,16 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
     AT_CUDA_TRY(cudaMalloc(&b->status, 4 * sizeof(uint32_t)));
     AT_CUDA_TRY(cudaMemset(b->status, 0, 4 * sizeof(uint32_t)));
     for (auto& e : b->ev) AT_CUDA_TRY(cudaEventCreate(&e));
-    AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<AT_ACT_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
-    AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<AT_ACT_GELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
-    AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<AT_ACT_SILU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
-    AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<AT_ACT_TANH>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
-    AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<AT_ACT_SIGMOID>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+#define AT_TOWER_ATTR(ACT_)                                                                                                     \
+  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
+  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
+  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+    AT_TOWER_ATTR(AT_ACT_RELU)
+    AT_TOWER_ATTR(AT_ACT_GELU)
+    AT_TOWER_ATTR(AT_ACT_SILU)
+    AT_TOWER_ATTR(AT_ACT_TANH)
+    AT_TOWER_ATTR(AT_ACT_SIGMOID)
+#undef AT_TOWER_ATTR
     AT_CUDA_TRY(cudaFuncSetAttribute(fc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fc_smem_bytes()));
     return AT_OK;
   };
@@ -739,6 +854,7 @@ void bf16_destroy(Bf16Path* b) {
   if (!b) return;
   for (int i = 0; i < 2; ++i) {
     cudaFree(b->wstream[i]);
+    cudaFree(b->wstream_pair[i]);
     cudaFree(b->wfc[i]);
     cudaFree(b->bias[i]);
     cudaFree(b->tfp[i]);
@@ -761,6 +877,11 @@ int bf16_pack_weights(Bf16Path* b, const Plan& p, const float* folded, int slot,
     const int K = b->layer_k[l], N = b->bias_w[l];
     pack_b_kernel<<<148, 256, 0, st>>>(folded + b->layer_wt[l], K, N, reinterpret_cast<__nv_bfloat16*>(b->wstream[slot] + off));
     AT_CUDA_TRY(cudaGetLastError());
+    if (b->wstream_pair[slot]) {
+      pack_b_split_kernel<<<148, 256, 0, st>>>(folded + b->layer_wt[l], K, N, b->layer_ks[l],
+                                               reinterpret_cast<__nv_bfloat16*>(b->wstream_pair[slot] + off));
+      AT_CUDA_TRY(cudaGetLastError());
+    }
     off += (size_t)K * N * 2;
   }
   pack_b_kernel<<<148 * 4, 256, 0, st>>>(folded + b->fc_wt, b->fc_flat, b->fc_n, reinterpret_cast<__nv_bfloat16*>(b->wfc[slot]));
@@ -837,12 +958,60 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
     if (tp.act0 == AT_ACT_RELU) tower_tf_kernel<AT_ACT_RELU><<<grid, kTfThreads, tower_tf_smem_bytes(), st>>>(t);
     else tower_tf_kernel<AT_ACT_GELU><<<grid, kTfThreads, tower_tf_smem_bytes(), st>>>(t);
   } else
-  switch (tp.act0) {
-    case AT_ACT_RELU: tower_kernel<AT_ACT_RELU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
-    case AT_ACT_GELU: tower_kernel<AT_ACT_GELU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
-    case AT_ACT_SILU: tower_kernel<AT_ACT_SILU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
-    case AT_ACT_TANH: tower_kernel<AT_ACT_TANH><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
-    default: tower_kernel<AT_ACT_SIGMOID><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
+  {
+    // CTA-pair mode (tcgen05 cta_group::2) unless AT_TOWER_PAIR=0: clusters of two CTAs, an even grid
+    const char* pm = getenv("AT_TOWER_MODE");
+    const int mode = pm ? atoi(pm) : 0;
+    const bool pair = mode == 1 && b->wstream_pair[slot] != nullptr && b->sms >= 2;
+    if (mode == 2) {
+      // same weight stream (chunk-major [K/8][N][8]); only the slab granularity changes: 32 K-values per slab
+      for (int l = 0; l < tp.n_layers; ++l) {
+        TowerLayer& L = tp.layers[l];
+        if (L.ks <= 32) continue;
+        L.ks = 32;
+        L.n_slabs = L.taps * L.cin / 32;
+        L.slab_bytes = 32u * (uint32_t)L.cout * 2u;
+        for (int sl = 0; sl < L.n_slabs && sl < kMaxSlabs; ++sl) {
+          const int k0 = sl * 32;
+          const int tap = k0 / L.cin, ch0 = k0 - tap * L.cin;
+          const int shift = L.taps == 9 ? (tap / 3 - 1) * kPadW + (tap % 3 - 1) : 0;
+          L.aoff[sl] = (uint32_t)((ch0 / 8) * kPlaneBytes + (kHalo + shift) * 16) >> 4;
+        }
+      }
+    }
+    cudaLaunchConfig_t cfg{};
+    cudaLaunchAttribute attr[1];
+    cfg.blockDim = dim3(kTowerThreads);
+    cfg.dynamicSmemBytes = tower_smem_bytes();
+    cfg.stream = st;
+    if (pair) {
+      tp.wstream = b->wstream_pair[slot];
+      unsigned g2 = (unsigned)(((n_pairs + 1) / 2) * 2);
+      const unsigned cap = (unsigned)(b->sms & ~1);
+      if (g2 > cap) g2 = cap;
+      cfg.gridDim = dim3(g2);
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = 2;
+      attr[0].val.clusterDim.y = 1;
+      attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+    } else {
+      cfg.gridDim = dim3(grid);
+    }
+#define AT_TOWER_LAUNCH(ACT_)                                                               \
+  if (pair) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 1>, tp));               \
+  else if (mode == 2) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 2>, tp));     \
+  else AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 0>, tp));
+    switch (tp.act0) {
+      case AT_ACT_RELU: AT_TOWER_LAUNCH(AT_ACT_RELU) break;
+      case AT_ACT_GELU: AT_TOWER_LAUNCH(AT_ACT_GELU) break;
+      case AT_ACT_SILU: AT_TOWER_LAUNCH(AT_ACT_SILU) break;
+      case AT_ACT_TANH: AT_TOWER_LAUNCH(AT_ACT_TANH) break;
+      default: AT_TOWER_LAUNCH(AT_ACT_SIGMOID) break;
+    }
+#undef AT_TOWER_LAUNCH
+    b->pair_mode = pair;
   }
   AT_CUDA_TRY(cudaGetLastError());
   AT_CUDA_TRY(cudaEventRecord(b->ev[1], st));
