@@ -134,6 +134,24 @@ __device__ __forceinline__ float act_fn(float x) {
   if constexpr (ACT == AT_ACT_RELU) return fmaxf(x, 0.0f);
   else return apply_act(x, ACT);
 }
+// eight fp32 values -> activation -> bf16, zeroed when `keep` is 0 (padding rows). ReLU commutes with the rounding, so it
+// is applied to the packed pairs (one HMNMX2 per two values) and the row mask is a single AND per pair.
+template <int ACT>
+__device__ __forceinline__ uint4 pack8_act(const float (&v)[8], uint32_t keep) {
+  uint32_t w[4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    if constexpr (ACT == AT_ACT_RELU) {
+      __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
+      h = __hmax2(h, __floats2bfloat162_rn(0.0f, 0.0f));
+      w[i] = *reinterpret_cast<uint32_t*>(&h) & keep;
+    } else {
+      w[i] = pack_bf16x2(act_fn<ACT>(v[2 * i]), act_fn<ACT>(v[2 * i + 1])) & keep;
+    }
+  }
+  return make_uint4(w[0], w[1], w[2], w[3]);
+}
+
 __device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
@@ -344,6 +362,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     const int m = q * 32 + lane;  // padded position = MMA row = TMEM lane
     const int y = m / kPadW, x = m % kPadW;
     const bool inside = (y < p.rows) && (x < p.cols);
+    const uint32_t keep = inside ? 0xFFFFFFFFu : 0u;
     const int pos = y * p.cols + x;  // compact position index (token order h*W + w)
     const uint32_t my_act_u = act_u + (uint32_t)eb * 2 * kBufBytes + (uint32_t)(kHalo + m) * 16;  // this row, plane 0, buffer 0
     const uint32_t tmem_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)eb * 128;
@@ -390,10 +409,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
             v[0] = fmaf(g[t], wa.x, v[0]); v[1] = fmaf(g[t], wa.y, v[1]); v[2] = fmaf(g[t], wa.z, v[2]); v[3] = fmaf(g[t], wa.w, v[3]);
             v[4] = fmaf(g[t], wb.x, v[4]); v[5] = fmaf(g[t], wb.y, v[5]); v[6] = fmaf(g[t], wb.z, v[6]); v[7] = fmaf(g[t], wb.w, v[7]);
           }
-#pragma unroll
-          for (int j = 0; j < 8; ++j) v[j] = inside ? act_fn<ACT>(v[j]) : 0.0f;
-          sts128(my_act_u + (uint32_t)(c8 / 8) * kPlaneBytes,
-                 make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7])));
+          sts128(my_act_u + (uint32_t)(c8 / 8) * kPlaneBytes, pack8_act<ACT>(v, keep));
         }
       }
       arrive_act();
@@ -429,9 +445,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
               v[0] += bf16_lo(rv.x); v[1] += bf16_hi(rv.x); v[2] += bf16_lo(rv.y); v[3] += bf16_hi(rv.y);
               v[4] += bf16_lo(rv.z); v[5] += bf16_hi(rv.z); v[6] += bf16_lo(rv.w); v[7] += bf16_hi(rv.w);
             }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) v[j] = inside ? act_fn<ACT>(v[j]) : 0.0f;
-            const uint4 out = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+            const uint4 out = pack8_act<ACT>(v, keep);
             if (to_smem) sts128(dst_u + (uint32_t)chunk * kPlaneBytes, out);
             else if (gstore) *reinterpret_cast<uint4*>(gdst + (size_t)chunk * 2048) = out;
           }

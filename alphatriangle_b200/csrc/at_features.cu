@@ -7,7 +7,8 @@
 // operations in the same order with explicitly rounded fp64 intrinsics (no FMA
 // contraction) and one __double2float_rn per feature. Result: bit-exact.
 //
-// HBM-bound: 80 B in + (Cg*R*C + D)*4 B out per state (680 B at the defaults).
+// HBM-bound: 80 B in + (Cg*R*C + D)*4 B out per state (680 B at the defaults). Boards up to 32 columns take
+// features_fast_kernel (bit-parallel rows, one thread per state); wider ones the generic kernel below it.
 // One block = 16 states; the 16 lanes of a state share its columns (heights, holes),
 // then its 30 float64 feature divisions, then its output rows (float4 stores).
 
@@ -175,6 +176,159 @@ __global__ void __launch_bounds__(kThreads) features_kernel(const PackedState* _
   }
 }
 
+
+// ---- fast path (COLS <= 32): one thread per state, whole board rows as bit masks -------------------------------
+//
+// heights / holes / bumpiness without a per-cell loop: with P_r = playable-occupied cells of row r as a bit mask and
+// G_r = P_r | P_{r+1} | ... (columns whose height exceeds r):
+//   sum(heights) = sum_r popc(G_r)        max(heights) = #{r : G_r != 0}
+//   holes        = sum_r popc(empty_r & G_{r+1})
+//   bumpiness    = sum_r popc((G_r ^ (G_r >> 1)) & low(cols-1))      (|h[c]-h[c+1]| = #rows where exactly one exceeds r)
+//
+// Divisions: every ratio except score/100 has small integer operands, and for integers |a|, b < 2^24
+//   float32(float64(a) / float64(b)) == float32(a) / float32(b)     (IEEE single division)
+// because a/b is at least 2^-49 (relative) away from every float32 rounding boundary it does not sit on, far more than
+// the 2^-53 the float64 rounding can move it; the same bound covers the reference's two-step quotients (a/b)/c = a/(bc)
+// and (0.75 w + 0.25)/cols = (3w+1)/(4 cols). tests/test_feature_identity.py checks the identity exhaustively over the
+// operand ranges a PackedState can carry. Clipping to [0,1] commutes with the final rounding (bounds are exact).
+constexpr int kFastThreads = 256;
+
+// bits [off, off + 32) of the 128-bit mask (lo, hi), masked to the board width; register-only (no indexed array)
+__device__ __forceinline__ uint32_t row_bits(uint64_t lo, uint64_t hi, int off, uint32_t mask) {
+  const uint64_t x = off < 64 ? lo : hi, y = off < 64 ? hi : 0ull;
+  const int sh = off & 63;
+  const uint64_t v = (x >> sh) | (sh ? (y << (64 - sh)) : 0ull);
+  return (uint32_t)v & mask;
+}
+__device__ __forceinline__ float ratio01(int a, int b) {  // clip(a / b, 0, 1) as the reference's float32 sees it
+  return fminf(fmaxf(__fdiv_rn((float)a, (float)b), 0.0f), 1.0f);
+}
+
+__global__ void __launch_bounds__(kFastThreads) features_fast_kernel(const PackedState* __restrict__ states, int64_t batch, int rows,
+                                                                      int cols, int slots, int grid_channels, int other_dim,
+                                                                      int vec_ok, float* __restrict__ grid, float* __restrict__ other) {
+  extern __shared__ __align__(16) uint8_t fsm[];
+  PackedState* s_state = reinterpret_cast<PackedState*>(fsm);
+  float* s_other = reinterpret_cast<float*>(fsm + kFastThreads * sizeof(PackedState));  // [state][other_dim]
+
+  const int tid = threadIdx.x;
+  const int64_t first = (int64_t)blockIdx.x * kFastThreads;
+  const int n_here = (int)min((int64_t)kFastThreads, batch - first);
+  {
+    const uint4* src = reinterpret_cast<const uint4*>(states + first);
+    uint4* dst = reinterpret_cast<uint4*>(s_state);
+    for (int i = tid; i < n_here * (AT_STATE_BYTES / 16); i += kFastThreads) dst[i] = __ldg(src + i);
+  }
+  __syncthreads();
+
+  const int cells = rows * cols;
+  const int n_full = slots * 8 + 6;
+  if (tid < n_here) {
+    const PackedState& st = s_state[tid];
+    uint32_t po[4], em[4];
+    int dead = 0;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const int lo = w * 32;
+      const uint32_t valid = cells >= lo + 32 ? 0xFFFFFFFFu : (cells > lo ? ((1u << (cells - lo)) - 1u) : 0u);
+      po[w] = st.occ[w] & ~st.death[w] & valid;
+      em[w] = ~st.occ[w] & ~st.death[w] & valid;
+      dead += __popc(st.death[w] & valid);
+    }
+    const uint64_t po_lo = po[0] | ((uint64_t)po[1] << 32), po_hi = po[2] | ((uint64_t)po[3] << 32);
+    const uint64_t em_lo = em[0] | ((uint64_t)em[1] << 32), em_hi = em[2] | ((uint64_t)em[3] << 32);
+    const uint32_t cmask = cols >= 32 ? 0xFFFFFFFFu : ((1u << cols) - 1u);
+    const uint32_t pmask = cmask >> 1;  // adjacent column pairs (c, c+1), c = 0 .. cols-2
+    uint32_t G = 0;
+    int sum_h = 0, max_h = 0, holes = 0, bump = 0;
+    for (int r = rows - 1; r >= 0; --r) {
+      holes += __popc(row_bits(em_lo, em_hi, r * cols, cmask) & G);
+      G |= row_bits(po_lo, po_hi, r * cols, cmask);
+      sum_h += __popc(G);
+      max_h += G != 0u;
+      bump += __popc((G ^ (G >> 1)) & pmask);
+    }
+    const int playable = cells - dead;
+    float* o = s_other + tid * other_dim;
+    auto put = [&](int d, float v) {
+      if (d < other_dim) o[d] = v;
+    };
+    for (int i = 0; i < slots; ++i) {  // _get_shape_features / _get_shape_availability (extractor.py:48-90)
+      const int8_t* sl = st.slot[i];
+      const int n = (int)(uint8_t)sl[1];
+      const bool present = sl[0] != 0;
+      float f[7] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+      if (present && n > 0) {
+        const int ups = (int)(uint8_t)sl[2];
+        const int min_r = sl[4], min_c = sl[5], max_r = sl[6], max_c = sl[7];
+        f[0] = ratio01(n, 5);
+        f[1] = __fdiv_rn((float)ups, (float)n);
+        f[2] = __fdiv_rn((float)(n - ups), (float)n);
+        f[3] = ratio01(max_r - min_r + 1, rows);
+        f[4] = ratio01(3 * (max_c - min_c + 1) + 1, 4 * cols);
+        f[5] = ratio01(min_r + max_r, 2 * rows);
+        f[6] = ratio01(min_c + max_c, 2 * cols);
+      }
+#pragma unroll
+      for (int k = 0; k < 7; ++k) put(i * 7 + k, f[k]);
+      put(slots * 7 + i, present ? 1.0f : 0.0f);
+    }
+    {  // _get_explicit_features (extractor.py:92-118)
+      const int e = slots * 8;
+      put(e + 0, store_f32(clip_d(__ddiv_rn(st.score, 100.0), -5.0, 5.0)));
+      put(e + 1, __fdiv_rn((float)sum_h, (float)(cols * rows)));
+      put(e + 2, __fdiv_rn((float)max_h, (float)rows));
+      put(e + 3, playable > 0 ? __fdiv_rn((float)holes, (float)playable) : 0.0f);
+      put(e + 4, cols > 1 ? __fdiv_rn((float)bump, (float)((cols - 1) * rows)) : 0.0f);
+      put(e + 5, st.step <= 0 ? 0.0f : (st.step >= 1000 ? 1.0f : __fdiv_rn((float)st.step, 1000.0f)));
+    }
+    for (int d = n_full; d < other_dim; ++d) o[d] = 0.0f;  // zero padding (extractor.py:127-139)
+  }
+  __syncthreads();
+
+  {  // other: the block's rows are one contiguous run
+    float* dst = other + first * other_dim;
+    const int total = n_here * other_dim;
+    if (vec_ok && (total & 3) == 0) {
+      const float4* s4 = reinterpret_cast<const float4*>(s_other);
+      float4* d4 = reinterpret_cast<float4*>(dst);
+      for (int i = tid; i < total / 4; i += kFastThreads) d4[i] = s4[i];
+    } else {
+      for (int i = tid; i < total; i += kFastThreads) dst[i] = s_other[i];
+    }
+  }
+  {  // grid: one warp per state and pass, each lane four cells (extractor.py:33-46)
+    const int per = grid_channels * cells;
+    const int warp = tid / 32, lane = tid % 32;
+    for (int ss = warp; ss < n_here; ss += kFastThreads / 32) {
+      const PackedState& st = s_state[ss];
+      float* dst = grid + (first + ss) * per;
+      if (vec_ok && (per & 3) == 0) {
+        for (int v4 = lane; v4 * 4 < per; v4 += 32) {
+          const int e0 = v4 * 4;
+          uint32_t on = 0, dn = 0;
+          if (e0 < cells) {  // four cells never straddle a 32-bit word
+            on = (st.occ[e0 >> 5] >> (e0 & 31)) & 0xFu;
+            dn = (st.death[e0 >> 5] >> (e0 & 31)) & 0xFu;
+            if (e0 + 4 > cells) {
+              const uint32_t keep = (1u << (cells - e0)) - 1u;
+              on &= keep;
+              dn &= keep;
+            }
+          }
+          float q[4];
+#pragma unroll
+          for (int j = 0; j < 4; ++j) q[j] = (dn >> j) & 1u ? -1.0f : ((on >> j) & 1u ? 1.0f : 0.0f);
+          *reinterpret_cast<float4*>(dst + e0) = make_float4(q[0], q[1], q[2], q[3]);
+        }
+      } else {
+        for (int e = lane; e < per; e += 32)
+          dst[e] = e < cells ? (bit_at(st.death, e) ? -1.0f : (bit_at(st.occ, e) ? 1.0f : 0.0f)) : 0.0f;
+      }
+    }
+  }
+}
+
 }  // namespace
 
 int launch_features(const at_env_desc& env, int grid_channels, int other_dim, const void* d_states, int64_t batch, float* d_grid,
@@ -190,6 +344,20 @@ int launch_features(const at_env_desc& env, int grid_channels, int other_dim, co
   const int64_t blocks = (batch + kStatesPerBlock - 1) / kStatesPerBlock;
   if (blocks > 0x7FFFFFFF) return fail(AT_E_INVALID, "at_extract_features: batch too large");
   // slot layout inside s_other: shape features at [i*7], availability at [slots*7+i], explicit at [slots*8]
+  if (env.cols <= 32) {
+    const int vec_ok = ((reinterpret_cast<uintptr_t>(d_grid) & 15u) == 0) && ((reinterpret_cast<uintptr_t>(d_other) & 15u) == 0) &&
+                       ((kFastThreads * other_dim) % 4 == 0) && ((grid_channels * env.rows * env.cols) % 4 == 0);
+    const size_t smem = (size_t)kFastThreads * (sizeof(PackedState) + (size_t)other_dim * sizeof(float));
+    if (smem <= 200 * 1024) {
+      if (smem > 48 * 1024) AT_CUDA_TRY(cudaFuncSetAttribute(features_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      const int64_t fblocks = (batch + kFastThreads - 1) / kFastThreads;
+      features_fast_kernel<<<(unsigned)fblocks, kFastThreads, smem, stream>>>(static_cast<const PackedState*>(d_states), batch, env.rows,
+                                                                              env.cols, env.slots, grid_channels, other_dim, vec_ok,
+                                                                              d_grid, d_other);
+      AT_CUDA_TRY(cudaGetLastError());
+      return AT_OK;
+    }
+  }
   const int grid_vec4 = ((grid_channels * env.rows * env.cols) % 4 == 0) && ((reinterpret_cast<uintptr_t>(d_grid) & 15u) == 0);
   features_kernel<<<(unsigned)blocks, kThreads, 0, stream>>>(static_cast<const PackedState*>(d_states), batch, env.rows, env.cols,
                                                               env.slots, grid_channels, other_dim, grid_vec4, d_grid, d_other);
