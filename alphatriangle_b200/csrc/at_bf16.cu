@@ -185,17 +185,34 @@ __device__ __forceinline__ void issue_slab(uint32_t tmem_base, uint32_t a0_16, u
   }
 }
 
+// one board only (board-independent pipelines, MODE 3)
+template <int NM>
+__device__ __forceinline__ void issue_slab1(uint32_t tmem_d, uint32_t a16, uint32_t b16, uint32_t a_lo_fixed, uint32_t b_lo_fixed,
+                                            uint32_t b_step16, uint32_t idesc, bool first) {
+  constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
+#pragma unroll
+  for (int j = 0; j < NM; ++j) {
+    const uint32_t a_lo = a_lo_fixed | (a16 + (uint32_t)j * (2 * kPlaneBytes >> 4));
+    const uint32_t b_lo = b_lo_fixed | (b16 + (uint32_t)j * b_step16);
+    mma_bf16(tmem_d, ((uint64_t)kDescHi << 32) | a_lo, ((uint64_t)kDescHi << 32) | b_lo, idesc, !(first && j == 0));
+  }
+}
+
 // ACT = the model-wide activation (every conv_block and ResidualBlock of a model shares it, model.py:127)
 // PAIR = two CTAs of a cluster drive one tensor-core pair (tcgen05 cta_group::2): every MMA covers board b of BOTH CTAs
 // (M = 256) and each CTA keeps only its half of the weight slab (N/2 rows of B), which halves the shared-memory reads
 // of B per SM and the L2 -> SM weight traffic. Rank 0 issues; rank 1's MMA warp only relays "my half has landed".
 // MODE 0: one CTA per SM, 4 ring stages of 16 KB (64 K-values per slab); MODE 1: CTA pairs, 8 stages of 8 KB (each CTA's half of
 // a 64-K slab); MODE 2: one CTA per SM, 8 stages of 8 KB (32 K-values per slab) -- twice as many slabs in flight.
+// MODE 3: like 0, but the two boards of a CTA are INDEPENDENT pipelines that only share the weight ring: one issuing warp and
+// eight epilogue warps per board, each board with its own accumulator / image-ready barriers. While one board's epilogue
+// drains its accumulator (tensor memory reads run at ~64 B/clock), the other board's MMAs keep the tensor pipe busy.
 template <int ACT, int MODE>
 __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_constant__ TowerParams p) {
   constexpr bool PAIR = MODE == 1;
-  constexpr int NS = MODE != 0 ? kStages2 : kStages;               // ring stages
-  constexpr uint32_t SB = MODE != 0 ? kStageBytes2 : kStageBytes;  // bytes per stage
+  constexpr bool SPLIT = MODE == 3;
+  constexpr int NS = (MODE == 1 || MODE == 2) ? kStages2 : kStages;               // ring stages
+  constexpr uint32_t SB = (MODE == 1 || MODE == 2) ? kStageBytes2 : kStageBytes;  // bytes per stage
   static_assert(NS * SB == kStages * kStageBytes, "both modes use the same ring footprint");
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* ring = smem;
@@ -215,6 +232,8 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   // accepts it, so a single issuer cannot overlap its per-slab bookkeeping (barrier wait, descriptors, commit: ~400 cycles)
   // with the 512 cycles its 8 MMAs run -- measured additive. With two issuers one warp's bookkeeping hides under the other's MMAs.
   constexpr int kIssuers = PAIR ? 1 : 2;
+  // MODE 3 barriers of board 1 (board 0 uses bar_acc / bar_act)
+  const uint32_t bar_acc1 = smem_u32(bars + 3 * NS + 3), bar_act1 = smem_u32(bars + 3 * NS + 4);
 
   // ---- one-time setup --------------------------------------------------------------------
   for (int i = tid; i < kBoards * 2 * kBufBytes / 16; i += kTowerThreads) reinterpret_cast<uint4*>(act)[i] = make_uint4(0, 0, 0, 0);
@@ -224,12 +243,14 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   if (tid == 0) {
     for (int i = 0; i < NS; ++i) {
       mbar_init(bar_full + 8 * i, 1);
-      mbar_init(bar_empty + 8 * i, 1);
+      mbar_init(bar_empty + 8 * i, SPLIT ? 2 : 1);  // MODE 3: both boards' issuers are done with the slab
       mbar_init(bar_full2 + 8 * i, 1);
     }
-    mbar_init(bar_acc, kIssuers);                          // every issuing warp commits its share of the layer
+    mbar_init(bar_acc, SPLIT ? 1 : kIssuers);             // every issuing warp commits its share of the layer
     mbar_init(bar_first, 1);
-    mbar_init(bar_act, PAIR ? 2 * kEpiWarps : kEpiWarps);  // one arrival per epilogue warp (of both CTAs in pair mode)
+    mbar_init(bar_act, PAIR ? 2 * kEpiWarps : (SPLIT ? kEpiWarps / 2 : kEpiWarps));  // one arrival per epilogue warp
+    mbar_init(bar_acc1, 1);
+    mbar_init(bar_act1, kEpiWarps / 2);
     fence_mbar_init();
   }
   if (warp == 0) {
@@ -286,7 +307,43 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     uint32_t phase = 0, act_phase = 0, first_phase = 0;
     bool ok = true;
     const uint32_t a_lo_fixed = (uint32_t)(kPlaneBytes >> 4) << 16;  // LBO = one 8-channel plane
-    if (PAIR && me != 0) {
+    if (SPLIT) {
+      // this warp drives board `me` only; every slab passes through both issuers and is released by the second commit
+      const uint32_t my_acc = me == 0 ? bar_acc : bar_acc1, my_act = me == 0 ? bar_act : bar_act1;
+      const uint32_t tmem_d = tmem_base + (uint32_t)me * 128;
+      for (int64_t lead = lead0; lead < n_pairs && ok; lead += gridDim.x) {
+        for (int l = 0; l < p.n_layers && ok; ++l) {
+          const TowerLayer& L = p.layers[l];
+          ok = __all_sync(0xffffffffu, wait_bar(my_act, act_phase, p.status, 2u));
+          if (!ok) break;
+          act_phase ^= 1;
+          tc_fence_after();
+          const uint32_t idesc = idesc_bf16(kM, (uint32_t)L.cout);
+          const uint32_t b_lbo16 = (uint32_t)L.cout, b_lo_fixed = b_lbo16 << 16;
+          const int mma_per_slab = L.ks / 16;
+          const uint32_t a_img16 = (act_u + (uint32_t)(me * 2 + L.src) * kBufBytes) >> 4;
+          for (int s = 0; s < L.n_slabs; ++s) {
+            const uint32_t a16 = a_img16 + L.aoff[s];
+            ok = __all_sync(0xffffffffu, wait_bar(bar_full + 8 * stage, phase, p.status, 4u));
+            if (!ok) break;
+            tc_fence_after();
+            const uint32_t b16 = (ring_u + stage * SB) >> 4;
+            if (elect_one()) {
+              if (!(p.debug & 2u)) {
+                if (mma_per_slab == 4) issue_slab1<4>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
+                else if (mma_per_slab == 2) issue_slab1<2>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
+                else issue_slab1<1>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
+              }
+              mma_commit(bar_empty + 8 * stage);
+            }
+            __syncwarp();
+            if (++stage == NS) { stage = 0; phase ^= 1; }
+          }
+          if (ok && elect_one()) mma_commit(my_acc);
+          __syncwarp();
+        }
+      }
+    } else if (PAIR && me != 0) {
       // pair mode keeps a single issuer
     } else if (PAIR && rank != 0) {
       // rank 1 of a pair issues nothing: it tells the leader when its half of each slab has landed
@@ -370,12 +427,14 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     bool ok = true;
     // "this layer's image is written": in pair mode every epilogue warp of both CTAs reports to the leader's barrier
     const uint32_t act_target = PAIR && rank != 0 ? mapa_smem(bar_act, 0) : bar_act;
+    const uint32_t my_act = SPLIT && eb == 1 ? bar_act1 : bar_act;
+    const uint32_t my_acc = SPLIT && eb == 1 ? bar_acc1 : bar_acc;
     auto arrive_act = [&]() {
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
         if (PAIR && rank != 0) mbar_arrive_remote(act_target);
-        else mbar_arrive(bar_act);
+        else mbar_arrive(my_act);
       }
     };
     for (int64_t lead = lead0, pair = pair0; lead < n_pairs && ok; lead += gridDim.x, pair += gridDim.x) {
@@ -416,7 +475,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
 
       for (int l = 0; l < p.n_layers; ++l) {
         const TowerLayer& L = p.layers[l];
-        ok = wait_bar(bar_acc, acc_phase, p.status, 8u);
+        ok = wait_bar(my_acc, acc_phase, p.status, 8u);
         if (!ok) break;
         acc_phase ^= 1;
         tc_fence_after();
@@ -617,7 +676,7 @@ __global__ void gather_bias_kernel(const float* __restrict__ folded, const int64
 
 constexpr size_t tower_tf_smem_bytes() {
   return (size_t)kTfStages * kStageBytes + (size_t)kBoards * 2 * kBufBytes + (size_t)kMaxLayers * 128 * 4 + 9 * 128 * 4 + 128 * 4 +
-         (size_t)kXchFloats * 4 + (2 * kStages + 2) * 8 + 16;
+         (size_t)kXchFloats * 4 + (2 * kStages + 4) * 8 + 16;
 }
 
 }  // namespace
@@ -845,7 +904,8 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
 #define AT_TOWER_ATTR(ACT_)                                                                                                     \
   AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
   AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
-  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
+  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
     AT_TOWER_ATTR(AT_ACT_RELU)
     AT_TOWER_ATTR(AT_ACT_GELU)
     AT_TOWER_ATTR(AT_ACT_SILU)
@@ -975,7 +1035,7 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
   {
     // CTA-pair mode (tcgen05 cta_group::2) unless AT_TOWER_PAIR=0: clusters of two CTAs, an even grid
     const char* pm = getenv("AT_TOWER_MODE");
-    const int mode = pm ? atoi(pm) : 0;
+    const int mode = pm ? atoi(pm) : 3;  // default: board-independent pipelines (see tower_kernel); 0/1/2 kept for experiments
     const bool pair = mode == 1 && b->wstream_pair[slot] != nullptr && b->sms >= 2;
     if (mode == 2) {
       // same weight stream (chunk-major [K/8][N][8]); only the slab granularity changes: 32 K-values per slab
@@ -1016,6 +1076,7 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
 #define AT_TOWER_LAUNCH(ACT_)                                                               \
   if (pair) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 1>, tp));               \
   else if (mode == 2) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 2>, tp));     \
+  else if (mode == 3) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 3>, tp));     \
   else AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 0>, tp));
     switch (tp.act0) {
       case AT_ACT_RELU: AT_TOWER_LAUNCH(AT_ACT_RELU) break;
