@@ -193,7 +193,8 @@ def run_ours(args):
     if world > 1:
         from alphatriangle_b200.dist import broadcast_weights
 
-        weight_bcast_ms = broadcast_weights(nn, src=0)
+        broadcast_weights(nn, src=0)                    # first call also builds the NCCL communicator
+        weight_bcast_ms = broadcast_weights(nn, src=0)  # steady state: one broadcast of the fp32 image + fold / repack on every rank
 
     # this rank's shard of the concurrent games (partitioned by game index; no data-path collective)
     states = synth_states(min(B, 1024), env, seed=1235 + rank)
