@@ -56,6 +56,7 @@ struct at_engine {
 
   Bf16Path* bf16 = nullptr;  // tcgen05 path state (null if the configuration is not covered)
   std::string bf16_reason;
+  uint2* heads_frag[2] = {nullptr, nullptr};  // per weight set: head matrices as bf16 MMA fragments (null: shape not covered)
 
   int64_t last_launches = 0;
 };
@@ -292,6 +293,34 @@ int64_t at_model_describe(const at_model_desc* desc, char* buf, int64_t cap) {
   return (int64_t)text.size();
 }
 
+// The fused head kernels' view of weight set `slot` (W = its folded image). Only for the one-shared-layer / one-hidden-
+// layer-per-head shape (the reference's defaults); the caller checks that first.
+static bool heads_shape_fused(const Plan& p) { return p.shared.size() == 1 && p.policy.size() == 2 && p.value.size() == 2; }
+
+static HeadsParams heads_params(const at_engine* e, const float* W, int slot) {
+  const Plan& p = e->plan;
+  const Affine& fc = p.shared[0];
+  HeadsParams hp{};
+  hp.other_dim = p.d.other_dim;
+  hp.w_other = W + fc.wt + (int64_t)p.flat * fc.N; hp.trunk_bias = W + fc.bias; hp.trunk_n = fc.N; hp.act = fc.act;
+  hp.wp1 = W + p.policy[0].wt; hp.bp1 = W + p.policy[0].bias; hp.wp2 = W + p.policy[1].wt; hp.bp2 = W + p.policy[1].bias;
+  hp.wv1 = W + p.value[0].wt; hp.bv1 = W + p.value[0].bias; hp.wv2 = W + p.value[1].wt; hp.bv2 = W + p.value[1].bias;
+  hp.pol_hidden = p.policy[0].N; hp.val_hidden = p.value[0].N; hp.actions = p.action_dim; hp.atoms = p.d.num_atoms;
+  hp.v_min = p.d.v_min; hp.v_max = p.d.v_max;
+  hp.frags = e->heads_frag[slot];
+  return hp;
+}
+
+// Trunk finish + heads + softmax epilogues in one launch: tensor-core variant when the packed fragments exist.
+static int run_heads_fused(at_engine* e, HeadsParams& hp, cudaStream_t st) {
+  static const bool cuda_core_heads = [] {  // AT_HEADS_MODE=0: the CUDA-core kernel, for A/B timing
+    const char* m = getenv("AT_HEADS_MODE");
+    return m && m[0] == '0';
+  }();
+  if (!cuda_core_heads && hp.frags && heads_mma_supported(hp)) return launch_heads_mma(hp, st, &e->last_launches);
+  return launch_heads_fused(hp, st, &e->last_launches);
+}
+
 int at_engine_create(const at_model_desc* desc, int device, int64_t max_batch, at_engine** out) {
   if (!desc || !out) return fail(AT_E_INVALID, "at_engine_create: null argument");
   *out = nullptr;
@@ -351,6 +380,13 @@ int at_engine_create(const at_model_desc* desc, int device, int64_t max_batch, a
   if (rc != AT_OK) { at_engine_destroy(e); return rc; }
   rc = bf16_create(p, max_batch, &e->bf16, &e->bf16_reason);
   if (rc != AT_OK) { at_engine_destroy(e); return rc; }
+  if (e->bf16 && heads_shape_fused(p)) {
+    const HeadsParams shape = heads_params(e, nullptr, 0);
+    if (heads_mma_supported(shape)) {
+      for (int i = 0; i < 2 && rc == AT_OK; ++i) rc = dev_alloc(&e->heads_frag[i], (int64_t)heads_frag_count(shape));
+      if (rc != AT_OK) { at_engine_destroy(e); return rc; }
+    }
+  }
   AT_CUDA_TRY(cudaDeviceSynchronize());
   *out = e;
   return AT_OK;
@@ -363,6 +399,7 @@ int at_engine_destroy(at_engine* e) {
   bf16_destroy(e->bf16);
   for (int i = 0; i < 2; ++i) {
     cudaFree(e->folded[i]);
+    cudaFree(e->heads_frag[i]);
     if (e->ready[i]) cudaEventDestroy(e->ready[i]);
     if (e->last_use[i]) cudaEventDestroy(e->last_use[i]);
   }
@@ -402,6 +439,10 @@ int at_engine_load_weights(at_engine* e, const float* d_image, int64_t n_floats,
   AT_CUDA_TRY(cudaStreamWaitEvent(st, e->last_use[target], 0));
   AT_TRY(fold_weights(e->plan, d_image, e->folded[target], st));
   if (e->bf16) AT_TRY(bf16_pack_weights(e->bf16, e->plan, e->folded[target], target, st));
+  if (e->heads_frag[target]) {
+    const HeadsParams hp = heads_params(e, e->folded[target], target);
+    AT_TRY(heads_pack_frags(hp, e->heads_frag[target], st));
+  }
   AT_CUDA_TRY(cudaEventRecord(e->ready[target], st));
   e->version[target] = version;
   e->active = target;
@@ -464,19 +505,12 @@ int at_engine_evaluate_packed_static(at_engine* e, const void* d_states, int64_t
   int splits = 0;
   const float *partial = nullptr, *other = nullptr;
   AT_TRY(bf16_trunk_partials_static(e->bf16, p, W, e->active, d_states, batch, &splits, &partial, &other, st, &e->last_launches));
-  const Affine& fc = p.shared[0];
-  HeadsParams hp{};
-  hp.partial = partial; hp.splits = splits;
-  hp.other = other; hp.other_dim = p.d.other_dim;
-  hp.w_other = W + fc.wt + (int64_t)p.flat * fc.N; hp.trunk_bias = W + fc.bias; hp.trunk_n = fc.N; hp.act = fc.act;
-  hp.wp1 = W + p.policy[0].wt; hp.bp1 = W + p.policy[0].bias; hp.wp2 = W + p.policy[1].wt; hp.bp2 = W + p.policy[1].bias;
-  hp.wv1 = W + p.value[0].wt; hp.bv1 = W + p.value[0].bias; hp.wv2 = W + p.value[1].wt; hp.bv2 = W + p.value[1].bias;
-  hp.pol_hidden = p.policy[0].N; hp.val_hidden = p.value[0].N; hp.actions = p.action_dim; hp.atoms = p.d.num_atoms;
-  hp.v_min = p.d.v_min; hp.v_max = p.d.v_max; hp.batch = batch;
+  HeadsParams hp = heads_params(e, W, e->active);
+  hp.partial = partial; hp.splits = splits; hp.other = other; hp.batch = batch;
   hp.probs = d_policy; hp.value = d_value; hp.flags = d_flags; hp.status = bf16_status_ptr(e->bf16);
   if (!heads_fused_supported(hp))
     return fail(AT_E_UNSUPPORTED, "at_engine_evaluate_packed_static: head widths outside what the fused head kernel covers");
-  AT_TRY(launch_heads_fused(hp, st, &e->last_launches));
+  AT_TRY(run_heads_fused(e, hp, st));
   return end_eval(e, st);
 }
 
@@ -522,19 +556,12 @@ int at_engine_evaluate_packed(at_engine* e, int precision, const void* d_states,
     if (batch > e->max_batch) return fail(AT_E_INVALID, "at_engine_evaluate_packed: batch exceeds the engine's max_batch");
     int splits = 0;
     AT_TRY(bf16_trunk_partials(e->bf16, p, W, e->active, d_states, batch, &splits, st, &e->last_launches));
-    if (p.shared.size() == 1 && p.policy.size() == 2 && p.value.size() == 2) {
-      const Affine& fc = p.shared[0];
-      HeadsParams hp{};
-      hp.partial = bf16_partial(e->bf16); hp.splits = splits;
-      hp.other = bf16_other(e->bf16); hp.other_dim = p.d.other_dim;
-      hp.w_other = W + fc.wt + (int64_t)p.flat * fc.N; hp.trunk_bias = W + fc.bias; hp.trunk_n = fc.N; hp.act = fc.act;
-      hp.wp1 = W + p.policy[0].wt; hp.bp1 = W + p.policy[0].bias; hp.wp2 = W + p.policy[1].wt; hp.bp2 = W + p.policy[1].bias;
-      hp.wv1 = W + p.value[0].wt; hp.bv1 = W + p.value[0].bias; hp.wv2 = W + p.value[1].wt; hp.bv2 = W + p.value[1].bias;
-      hp.pol_hidden = p.policy[0].N; hp.val_hidden = p.value[0].N; hp.actions = p.action_dim; hp.atoms = p.d.num_atoms;
-      hp.v_min = p.d.v_min; hp.v_max = p.d.v_max; hp.batch = batch;
+    if (heads_shape_fused(p)) {
+      HeadsParams hp = heads_params(e, W, e->active);
+      hp.partial = bf16_partial(e->bf16); hp.splits = splits; hp.other = bf16_other(e->bf16); hp.batch = batch;
       hp.probs = d_policy; hp.value = d_value; hp.flags = d_flags; hp.status = bf16_status_ptr(e->bf16);
       if (heads_fused_supported(hp)) {
-        AT_TRY(launch_heads_fused(hp, st, &e->last_launches));
+        AT_TRY(run_heads_fused(e, hp, st));
         return end_eval(e, st);
       }
     }

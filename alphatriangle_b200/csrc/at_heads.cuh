@@ -26,10 +26,18 @@ struct HeadsParams {
   uint32_t* flags;
   int w_stage_off;         // filled by the launcher: float offset of the weight staging area in shared memory
   const uint32_t* status;  // optional: tcgen05 pipeline status word folded into the flags
+  const uint2* frags;      // tensor-core variant: the four head matrices as bf16 mma.sync B fragments (heads_pack_frags), else null
 };
 
 size_t heads_fused_smem(const HeadsParams& p);
 bool heads_fused_supported(const HeadsParams& p);
 int launch_heads_fused(const HeadsParams& p, cudaStream_t stream, int64_t* launches);
+
+// Tensor-core variant (heads_mma_kernel): same inputs and outputs, the four head GEMMs on warp-level bf16 MMAs with the
+// weights pre-packed into B-fragment order (one coalesced 256-byte load per 16x8 tile, no shared-memory staging).
+bool heads_mma_supported(const HeadsParams& p);
+size_t heads_frag_count(const HeadsParams& p);  // uint2 elements of the packed image
+int heads_pack_frags(const HeadsParams& p, uint2* dst, cudaStream_t stream);  // from p.wp1 / wv1 / wp2 / wv2
+int launch_heads_mma(const HeadsParams& p, cudaStream_t stream, int64_t* launches);
 
 }  // namespace at

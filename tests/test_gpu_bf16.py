@@ -80,10 +80,16 @@ def test_bf16_full_batch_rows_are_independent(case, golden_dir):
     probs, value = nn.evaluate_packed(torch.from_numpy(packed).cuda())
     p0, v0 = nn.evaluate_packed(torch.from_numpy(base).cuda())
     idx = np.arange(4096) % base.shape[0]
-    # the tower is bitwise per board; only the split-K factor of the trunk FC depends on the batch size,
-    # so the two runs may differ by fp32 summation order and nothing more
-    assert np.abs(probs.cpu().numpy() - p0.cpu().numpy()[idx]).max() <= 1e-6
-    assert np.abs(value.cpu().numpy() - v0.cpu().numpy()[idx]).max() <= 1e-4
+    probs, value, p0, v0 = probs.cpu().numpy(), value.cpu().numpy(), p0.cpu().numpy(), v0.cpu().numpy()
+    # inside one launch the same board gives the same bits wherever it sits in the batch
+    n = base.shape[0]
+    assert np.array_equal(probs, probs[:n][idx])
+    assert np.array_equal(value, value[:n][idx])
+    # against a small batch only the split-K factor of the trunk FC differs: fp32 summation order, which can move a
+    # trunk activation across a bf16 rounding boundary (one ulp = 0.4 %) before the head GEMMs -- nothing larger
+    assert np.abs(probs - p0[idx]).max() <= 1e-3
+    assert np.abs(value - v0[idx]).max() <= 5e-2
+    assert kl_rows(p0[idx], probs).max() <= 1e-5
 
 
 def test_bf16_through_the_drop_in_api(golden_dir):
