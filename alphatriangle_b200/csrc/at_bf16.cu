@@ -1002,11 +1002,13 @@ int bf16_pack_weights(Bf16Path* b, const Plan& p, const float* folded, int slot,
 }
 
 int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slot, const void* d_states, int64_t batch, int* n_splits,
-                        cudaStream_t st, int64_t* launches) {
+                        cudaStream_t st, int64_t* launches, bool with_other) {
   const at_model_desc& d = p.d;
-  // "other" features for the FC's last columns (the grid output of this launch is not used by the tower)
-  AT_TRY(launch_features(d.env, 1, d.other_dim, d_states, batch, b->grid, b->other, st));
-  ++*launches;
+  if (with_other) {
+    // "other" features for the FC's last columns (the grid output of this launch is not used by the tower)
+    AT_TRY(launch_features(d.env, 1, d.other_dim, d_states, batch, b->grid, b->other, st));
+    ++*launches;
+  }
 
   TowerParams tp = b->tp;
   tp.states = static_cast<const PackedState*>(d_states);

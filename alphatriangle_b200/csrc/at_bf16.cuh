@@ -16,9 +16,10 @@ void bf16_destroy(Bf16Path* p);
 // folded fp32 set -> bf16 operand images for weight set `slot` (0/1)
 int bf16_pack_weights(Bf16Path* p, const Plan& plan, const float* d_folded, int slot, cudaStream_t stream);
 // PackedState[batch] -> split-K partial sums of the first shared FC layer over the tower output, fp32
-// [n_splits][batch][shared[0].N] (bf16_partial), plus the "other" feature vectors (bf16_other)
+// [n_splits][batch][shared[0].N] (bf16_partial), plus -- unless the consumer derives them itself from the packed
+// states (with_other = false) -- the "other" feature vectors (bf16_other)
 int bf16_trunk_partials(Bf16Path* p, const Plan& plan, const float* d_folded, int slot, const void* d_states, int64_t batch,
-                        int* n_splits, cudaStream_t stream, int64_t* launches);
+                        int* n_splits, cudaStream_t stream, int64_t* launches, bool with_other = true);
 const float* bf16_partial(const Bf16Path* p);
 const float* bf16_other(const Bf16Path* p);
 // partials + other columns + bias, activation -> d_trunk fp32 [batch, shared[0].N] (unfused tail, also the test hook)

@@ -311,13 +311,23 @@ static HeadsParams heads_params(const at_engine* e, const float* W, int slot) {
   return hp;
 }
 
+// AT_HEADS_MODE=0: the CUDA-core head kernel; 1: tensor-core heads fed by the feature kernel (A/B timing only)
+static int heads_mode() {
+  static const int mode = [] {
+    const char* m = getenv("AT_HEADS_MODE");
+    return (m && m[0] >= '0' && m[0] <= '2') ? m[0] - '0' : 2;
+  }();
+  return mode;
+}
+
+static bool heads_use_mma(const HeadsParams& hp) { return heads_mode() != 0 && hp.frags && heads_mma_supported(hp); }
+static bool heads_take_states(const at_engine* e, const HeadsParams& hp) {
+  return heads_mode() == 2 && heads_use_mma(hp) && heads_fused_supported(hp) && e->plan.d.env.cols <= 32;
+}
+
 // Trunk finish + heads + softmax epilogues in one launch: tensor-core variant when the packed fragments exist.
 static int run_heads_fused(at_engine* e, HeadsParams& hp, cudaStream_t st) {
-  static const bool cuda_core_heads = [] {  // AT_HEADS_MODE=0: the CUDA-core kernel, for A/B timing
-    const char* m = getenv("AT_HEADS_MODE");
-    return m && m[0] == '0';
-  }();
-  if (!cuda_core_heads && hp.frags && heads_mma_supported(hp)) return launch_heads_mma(hp, st, &e->last_launches);
+  if (heads_use_mma(hp)) return launch_heads_mma(hp, st, &e->last_launches);
   return launch_heads_fused(hp, st, &e->last_launches);
 }
 
@@ -555,10 +565,16 @@ int at_engine_evaluate_packed(at_engine* e, int precision, const void* d_states,
   if (precision == AT_PREC_BF16) {
     if (batch > e->max_batch) return fail(AT_E_INVALID, "at_engine_evaluate_packed: batch exceeds the engine's max_batch");
     int splits = 0;
-    AT_TRY(bf16_trunk_partials(e->bf16, p, W, e->active, d_states, batch, &splits, st, &e->last_launches));
+    // the tensor-core head kernel derives the other-feature vectors itself: no separate feature launch on this path
+    const bool heads_own_other = heads_shape_fused(p) && heads_take_states(e, heads_params(e, W, e->active));
+    AT_TRY(bf16_trunk_partials(e->bf16, p, W, e->active, d_states, batch, &splits, st, &e->last_launches, !heads_own_other));
     if (heads_shape_fused(p)) {
       HeadsParams hp = heads_params(e, W, e->active);
       hp.partial = bf16_partial(e->bf16); hp.splits = splits; hp.other = bf16_other(e->bf16); hp.batch = batch;
+      if (heads_own_other) {
+        hp.states = static_cast<const PackedState*>(d_states);
+        hp.env_rows = p.d.env.rows; hp.env_cols = p.d.env.cols; hp.env_slots = p.d.env.slots;
+      }
       hp.probs = d_policy; hp.value = d_value; hp.flags = d_flags; hp.status = bf16_status_ptr(e->bf16);
       if (heads_fused_supported(hp)) {
         AT_TRY(run_heads_fused(e, hp, st));

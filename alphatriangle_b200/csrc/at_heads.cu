@@ -12,6 +12,7 @@
 
 #include <cuda_bf16.h>
 
+#include "at_features.cuh"
 #include "at_fp32.cuh"
 #include "at_heads.cuh"
 
@@ -431,9 +432,26 @@ __global__ void __launch_bounds__(kMmaThreads, 1) heads_mma_kernel(const HeadsPa
   const FragLayout L = frag_layout(p);
 
   // ---- trunk: split-K partials + other-feature columns + bias, activation -> bf16 ----
-  for (int i = tid; i < TB * p.other_dim; i += kMmaThreads) {
-    const int b = i / p.other_dim;
-    o_s[i] = b < n_here ? p.other[b0 * p.other_dim + i] : 0.0f;
+  if (p.states) {
+    // other features straight from the packed records: stage the block's 32 states (the trunk tile is still unused),
+    // then one thread per board (extractor.py:48-139, shared with the feature kernel)
+    PackedState* st_s = reinterpret_cast<PackedState*>(t_s);
+    const uint4* src = reinterpret_cast<const uint4*>(p.states + b0);
+    for (int i = tid; i < n_here * (AT_STATE_BYTES / 16); i += kMmaThreads) reinterpret_cast<uint4*>(st_s)[i] = __ldg(src + i);
+    __syncthreads();
+    if (tid < TB) {
+      float* o = o_s + tid * p.other_dim;
+      if (tid < n_here) {
+        other_features_bits(st_s[tid], p.env_rows, p.env_cols, p.env_slots, p.other_dim, o);
+      } else {
+        for (int d = 0; d < p.other_dim; ++d) o[d] = 0.0f;
+      }
+    }
+  } else {
+    for (int i = tid; i < TB * p.other_dim; i += kMmaThreads) {
+      const int b = i / p.other_dim;
+      o_s[i] = b < n_here ? p.other[b0 * p.other_dim + i] : 0.0f;
+    }
   }
   __syncthreads();
   {
@@ -574,6 +592,9 @@ int heads_pack_frags(const HeadsParams& p, uint2* dst, cudaStream_t stream) {
 int launch_heads_mma(const HeadsParams& p, cudaStream_t stream, int64_t* launches) {
   if (p.batch <= 0) return AT_OK;
   if (!p.frags) return fail(AT_E_INVALID, "launch_heads_mma: packed head weights missing");
+  if (p.states && (p.env_cols > 32 || p.env_rows * p.env_cols > AT_MAX_CELLS || (size_t)TB * AT_STATE_BYTES > (size_t)TB * (p.trunk_n + kPadH) * 2))
+    return fail(AT_E_INVALID, "launch_heads_mma: in-kernel other features need a board of at most 32 columns");
+  if (!p.states && !p.other) return fail(AT_E_INVALID, "launch_heads_mma: neither other features nor packed states given");
   const size_t smem = heads_mma_smem(p);
   const unsigned grid = (unsigned)((p.batch + TB - 1) / TB);
   // the opt-in is per device and cheap; set on every launch so several engines on different GPUs stay correct

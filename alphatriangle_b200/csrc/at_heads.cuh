@@ -27,6 +27,10 @@ struct HeadsParams {
   int w_stage_off;         // filled by the launcher: float offset of the weight staging area in shared memory
   const uint32_t* status;  // optional: tcgen05 pipeline status word folded into the flags
   const uint2* frags;      // tensor-core variant: the four head matrices as bf16 mma.sync B fragments (heads_pack_frags), else null
+  // tensor-core variant, optional: derive the other-feature vectors from the packed states in the prologue instead of
+  // reading `other` (same arithmetic as the feature kernel, at_features.cuh); needs env_cols <= 32
+  const PackedState* states;
+  int env_rows, env_cols, env_slots;
 };
 
 size_t heads_fused_smem(const HeadsParams& p);
