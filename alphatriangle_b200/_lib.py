@@ -53,6 +53,7 @@ EXPORTS = (
     "at_engine_action_dim",
     "at_probe_umma",
     "at_probe_umma_ts",
+    "at_probe_mma_rate",
 )
 
 
@@ -126,6 +127,7 @@ def _bind(lib: C.CDLL) -> None:
         "at_engine_kernel_ms": (i32, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
         "at_engine_action_dim": (i32, [vp]),
         "at_probe_umma_ts": (i32, [vp, vp, i64, i32, i32, i32, u32, u32, u32, u32, u32, u32, vp, vp, vp]),
+        "at_probe_mma_rate": (i32, [i32, i32, i32, i32, i32, vp, i32, vp, vp]),
         "at_probe_umma": (i32, [vp, i64, vp, i64, i32, i32, u32, u32, u32, u32, u32, u32, u32, u32, i32, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():

@@ -51,8 +51,8 @@ constexpr int kBoards = 2;                   // boards in flight per CTA
 constexpr int kEpiSplit = 2;                 // epilogue warps per (board, TMEM lane quarter): each takes 1/kEpiSplit of the channels
 constexpr int kEpiWarps = kBoards * 4 * kEpiSplit;
 constexpr int kMmaWarpB = 2 + kEpiWarps;      // second MMA-issuing warp (odd slabs); warp 1 takes the even ones
-constexpr int kTowerThreads = 64 + kEpiWarps * 32 + 32;
-constexpr int kMaxBars = 32;                 // mbarrier slots reserved in shared memory
+constexpr int kTowerThreads = 64 + kEpiWarps * 32 + 32 + 64;  // + two more issuing warps (MODE 5 / 6)
+constexpr int kMaxBars = 40;                 // mbarrier slots reserved in shared memory
 // CTA-pair mode (cta_group::2): each CTA streams half of every weight slab, so stages are half as big and twice as many
 constexpr int kStages2 = 8;
 constexpr int kStageBytes2 = 8192;
@@ -67,6 +67,11 @@ struct TowerLayer {
   // where each weight slab's first MMA reads its A operand, relative to the source image, >> 4: the slab covers channels
   // [c0, c0 + ks) of one tap, i.e. plane c0/8 of the image shifted by (dy*16 + dx) rows
   uint32_t aoff[kMaxSlabs];
+  // MODE 4: ring order. Slab s of the ring is slab slab_src[s] of the packed stream (aoff is already in ring order): the slabs
+  // that read input channels < 64 come first, so they can run while the producer layer's epilogue still writes channels >= 64.
+  // half_slab = first ring slab that needs channels >= 64 (n_slabs if none does).
+  uint8_t slab_src[kMaxSlabs];
+  int half_slab;
 };
 
 struct TowerParams {
@@ -101,6 +106,21 @@ __device__ __forceinline__ bool wait_bar(uint32_t bar, uint32_t parity, uint32_t
   if (mbar_try_wait(bar, parity)) return true;  // common case: no clock reads on the fast path
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
+    if (clock64() - t0 > kTimeoutCycles) {
+      atomicOr(status, code);
+      return false;
+    }
+  }
+  return true;
+}
+
+// Busy-polling flavour for the warps on the per-slab critical path (weight producer, MMA issuers): test_wait never parks
+// the thread, so the wake-up after the phase flips costs one poll instead of the hardware's suspend granularity.
+__device__ __forceinline__ bool wait_bar_spin(uint32_t bar, uint32_t parity, uint32_t* status, uint32_t code) {
+  for (int i = 0; i < 64; ++i)
+    if (mbar_test_wait(bar, parity)) return true;
+  const long long t0 = clock64();
+  while (!mbar_test_wait(bar, parity)) {
     if (clock64() - t0 > kTimeoutCycles) {
       atomicOr(status, code);
       return false;
@@ -207,10 +227,21 @@ __device__ __forceinline__ void issue_slab1(uint32_t tmem_d, uint32_t a16, uint3
 // MODE 3: like 0, but the two boards of a CTA are INDEPENDENT pipelines that only share the weight ring: one issuing warp and
 // eight epilogue warps per board, each board with its own accumulator / image-ready barriers. While one board's epilogue
 // drains its accumulator (tensor memory reads run at ~64 B/clock), the other board's MMAs keep the tensor pipe busy.
+// MODE 4: MODE 3 + overlap inside a board. Both boards walk the shared weight ring within four slabs of each other, so their
+// epilogues coincide and the tensor pipe idles meanwhile. Here every board has TWO accumulators (layers alternate) and the
+// "image written" signal is split by channel half: the epilogue reports channels 0-63 after its first pass, and the next
+// layer -- whose slabs are streamed lower-channel-half first -- starts accumulating into the other accumulator while the
+// second pass (channels 64-127) is still draining tensor memory. Half of every epilogue disappears under MMAs.
+// MODE 5: MODE 3 with TWO issuing warps per board taking alternate slabs: the ~90 instructions of per-slab bookkeeping (barrier
+// wait, descriptor arithmetic, commit) are a dependent chain of ~450 cycles in one warp -- as long as the four MMAs it
+// feeds -- and the issue itself blocks while the pipe is busy; with a sibling warp the bookkeeping of slab s+1 runs under
+// the MMAs of slab s. MODE 6 = 5 + 4.
 template <int ACT, int MODE>
 __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_constant__ TowerParams p) {
   constexpr bool PAIR = MODE == 1;
-  constexpr bool SPLIT = MODE == 3;
+  constexpr bool SPLIT = MODE >= 3;
+  constexpr bool PP = MODE == 4 || MODE == 6;  // two accumulators per board + channel-half hand-off (see the comment above)
+  constexpr bool QUAD = MODE >= 5;             // two issuing warps per board, alternate slabs (see the comment above)
   constexpr int NS = (MODE == 1 || MODE == 2) ? kStages2 : kStages;               // ring stages
   constexpr uint32_t SB = (MODE == 1 || MODE == 2) ? kStageBytes2 : kStageBytes;  // bytes per stage
   static_assert(NS * SB == kStages * kStageBytes, "both modes use the same ring footprint");
@@ -234,6 +265,10 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   constexpr int kIssuers = PAIR ? 1 : 2;
   // MODE 3 barriers of board 1 (board 0 uses bar_acc / bar_act)
   const uint32_t bar_acc1 = smem_u32(bars + 3 * NS + 3), bar_act1 = smem_u32(bars + 3 * NS + 4);
+  // MODE 4: "channels >= 64 of the image are written", per board (bar_act / bar_act1 then mean channels < 64)
+  const uint32_t bar_hi0 = smem_u32(bars + 3 * NS + 5), bar_hi1 = smem_u32(bars + 3 * NS + 6);
+  // MODE 5/6: "the layer's first (overwriting) MMA of this board is in the pipe", per board
+  const uint32_t bar_first0 = smem_u32(bars + 3 * NS + 7), bar_first1 = smem_u32(bars + 3 * NS + 8);
 
   // ---- one-time setup --------------------------------------------------------------------
   for (int i = tid; i < kBoards * 2 * kBufBytes / 16; i += kTowerThreads) reinterpret_cast<uint4*>(act)[i] = make_uint4(0, 0, 0, 0);
@@ -246,11 +281,15 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
       mbar_init(bar_empty + 8 * i, SPLIT ? 2 : 1);  // MODE 3: both boards' issuers are done with the slab
       mbar_init(bar_full2 + 8 * i, 1);
     }
-    mbar_init(bar_acc, SPLIT ? 1 : kIssuers);             // every issuing warp commits its share of the layer
+    mbar_init(bar_acc, QUAD ? 2 : (SPLIT ? 1 : kIssuers));  // every issuing warp commits its share of the layer
     mbar_init(bar_first, 1);
     mbar_init(bar_act, PAIR ? 2 * kEpiWarps : (SPLIT ? kEpiWarps / 2 : kEpiWarps));  // one arrival per epilogue warp
-    mbar_init(bar_acc1, 1);
+    mbar_init(bar_acc1, QUAD ? 2 : 1);
+    mbar_init(bar_first0, 1);
+    mbar_init(bar_first1, 1);
     mbar_init(bar_act1, kEpiWarps / 2);
+    mbar_init(bar_hi0, kEpiWarps / 2);
+    mbar_init(bar_hi1, kEpiWarps / 2);
     fence_mbar_init();
   }
   if (warp == 0) {
@@ -258,7 +297,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
       tmem_alloc2(smem_u32(tmem_slot), kBoards * 128);
       tmem_relinquish2();
     } else {
-      tmem_alloc(smem_u32(tmem_slot), kBoards * 128);
+      tmem_alloc(smem_u32(tmem_slot), PP ? 2 * kBoards * 128 : kBoards * 128);
       tmem_relinquish();
     }
   }
@@ -274,9 +313,45 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   const int64_t pair0 = blockIdx.x;
   const int64_t lead0 = PAIR ? (int64_t)(blockIdx.x & ~1u) : (int64_t)blockIdx.x;
 
-  if (warp == 0) {
+  if (QUAD && warp == 0) {
+    // ===== weight producer, MODE 5/6: lane i owns ring stage i and streams slabs i, i+NS, ... of the pair's slab sequence.
+    // The per-slab chain (barrier wait, expect_tx, bulk copy: ~400 cycles of dependent long-latency operations in one thread)
+    // then runs for NS slabs at once. =====
+    if (lane < NS) {
+      int l = 0, s = lane;
+      int64_t lead = lead0;
+      uint32_t base = 0, phase = 0;
+      auto settle = [&]() {  // carry the cursor over layer / board-pair ends
+        while (lead < n_pairs && s >= p.layers[l].n_slabs) {
+          s -= p.layers[l].n_slabs;
+          base += (uint32_t)p.layers[l].n_slabs * p.layers[l].slab_bytes;
+          if (++l == p.n_layers) {
+            l = 0;
+            base = 0;
+            lead += gridDim.x;
+          }
+        }
+      };
+      settle();
+      const uint32_t my_full = bar_full + 8 * lane, my_empty = bar_empty + 8 * lane, my_ring = ring_u + lane * SB;
+      while (lead < n_pairs) {
+        const TowerLayer& L = p.layers[l];
+        if (!wait_bar(my_empty, phase ^ 1, p.status, 1u)) break;
+        if (p.debug & 1u) {
+          mbar_arrive(my_full);
+        } else {
+          const uint32_t bytes = L.slab_bytes;
+          mbar_arrive_expect_tx(my_full, bytes);
+          bulk_g2s(my_ring, p.wstream + base + (uint32_t)(PP ? (int)L.slab_src[s] : s) * bytes, bytes, my_full);
+        }
+        phase ^= 1;
+        s += NS;
+        settle();
+      }
+    }
+  } else if (warp == 0) {
     // ===== weight producer: one lane streams every layer's slabs through the ring =====
-    if (lane == 0) {
+    if (lane == 0 && !(p.debug & 8192u)) {
       int stage = 0;
       uint32_t phase = 0;
       bool ok = true;
@@ -286,13 +361,15 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
           const uint32_t slab = p.layers[l].slab_bytes;
           const uint32_t bytes = PAIR ? slab / 2 : slab;  // pair mode: this CTA's N/2 rows, stored as [slab][half]
           for (int s = 0; s < p.layers[l].n_slabs; ++s) {
-            ok = wait_bar(bar_empty + 8 * stage, phase ^ 1, p.status, 1u);
+            ok = (p.debug & 4096u) ? wait_bar_spin(bar_empty + 8 * stage, phase ^ 1, p.status, 1u)
+                                   : wait_bar(bar_empty + 8 * stage, phase ^ 1, p.status, 1u);
             if (!ok) break;
             if (p.debug & 1u) {
               mbar_arrive(bar_full + 8 * stage);
             } else {
               mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
-              bulk_g2s(ring_u + stage * SB, src + (PAIR ? rank * bytes : 0u), bytes, bar_full + 8 * stage);
+              const uint8_t* from = PP ? src + ((int)p.layers[l].slab_src[s] - s) * (int64_t)slab : src + (PAIR ? rank * bytes : 0u);
+              bulk_g2s(ring_u + stage * SB, from, bytes, bar_full + 8 * stage);
             }
             src += slab;
             if (++stage == NS) { stage = 0; phase ^= 1; }
@@ -300,6 +377,78 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         }
       }
     }
+  } else if (QUAD && (warp == 1 || warp >= kMmaWarpB)) {
+    // ===== MODE 5/6 issuers: warp (board me, parity par) takes the board's slabs par, par+2, ... of every layer. One thread
+    // runs the whole loop: nothing here needs the other lanes, and votes / elections per slab only lengthen the chain. =====
+    const int wi = warp == 1 ? 0 : warp - kMmaWarpB + 1;
+    const int me = wi & 1, par = wi >> 1;
+    if (lane == 0) {
+      const uint32_t my_acc = me == 0 ? bar_acc : bar_acc1, my_act = me == 0 ? bar_act : bar_act1, my_hi = me == 0 ? bar_hi0 : bar_hi1;
+      const uint32_t my_first = me == 0 ? bar_first0 : bar_first1;
+      const uint32_t tmem_board = tmem_base + (uint32_t)me * (PP ? 256 : 128);
+      const uint32_t a_lo_fixed = (uint32_t)(kPlaneBytes >> 4) << 16;  // LBO = one 8-channel plane
+      const bool no_mma = (p.debug & 2u) != 0;
+      uint32_t g = 0;       // ring slabs this board has passed (every issuer counts all of them)
+      uint32_t lphase = 0;  // parity of the per-layer barriers
+      uint32_t acc_sel = 0;
+      bool ok = true;
+      for (int64_t lead = lead0; lead < n_pairs && ok; lead += gridDim.x) {
+        for (int l = 0; l < p.n_layers && ok; ++l) {
+          const TowerLayer& L = p.layers[l];
+          const int n_slabs = L.n_slabs;
+          const int half = PP ? L.half_slab : 0;
+          ok = wait_bar(my_act, lphase, p.status, 2u);
+          if (!ok) break;
+          bool hi_seen = !PP;
+          if (PP && half == 0) {
+            ok = wait_bar(my_hi, lphase, p.status, 2u);
+            if (!ok) break;
+            hi_seen = true;
+          }
+          if (par == 1) {  // never accumulate onto the previous layer's sums: slab 0 (accumulate off) goes first
+            ok = wait_bar(my_first, lphase, p.status, 2u);
+            if (!ok) break;
+          }
+          tc_fence_after();
+          const uint32_t tmem_d = tmem_board + acc_sel * 128u;
+          const uint32_t idesc = idesc_bf16(kM, (uint32_t)L.cout);
+          const uint32_t b_lbo16 = (uint32_t)L.cout, b_lo_fixed = b_lbo16 << 16;
+          const int mma_per_slab = no_mma ? 0 : L.ks / 16;
+          const uint32_t a_img16 = (act_u + (uint32_t)(me * 2 + L.src) * kBufBytes) >> 4;
+          uint32_t a_next = par < n_slabs ? L.aoff[par] : 0u;
+          for (int s = par; s < n_slabs; s += 2) {
+            if (PP && !hi_seen && s >= half) {
+              ok = wait_bar(my_hi, lphase, p.status, 2u);
+              if (!ok) break;
+              hi_seen = true;
+            }
+            const uint32_t gs = g + (uint32_t)s, stage = gs % NS, ph = (gs / NS) & 1u;
+            const uint32_t a16 = a_img16 + a_next;
+            if (s + 2 < n_slabs) a_next = L.aoff[s + 2];  // the next slab's offset is in flight while this one is issued
+            ok = wait_bar(bar_full + 8 * stage, ph, p.status, 4u);
+            if (!ok) break;
+            tc_fence_after();
+            const uint32_t b16 = (ring_u + stage * SB) >> 4;
+            if (mma_per_slab == 4) issue_slab1<4>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
+            else if (mma_per_slab == 2) issue_slab1<2>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
+            else if (mma_per_slab == 1) issue_slab1<1>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
+            mma_commit(bar_empty + 8 * stage);
+            if (s == 0) mbar_arrive(my_first);
+          }
+          if (!ok) break;
+          if (PP && !hi_seen) {  // keep the barrier phases paired
+            ok = wait_bar(my_hi, lphase, p.status, 2u);
+            if (!ok) break;
+          }
+          mma_commit(my_acc);
+          g += (uint32_t)n_slabs;
+          lphase ^= 1u;
+          if (PP) acc_sel ^= 1u;
+        }
+      }
+    }
+  } else if (warp > kMmaWarpB) {
+    // the extra issuing warps idle in the other modes
   } else if (warp == 1 || warp == kMmaWarpB) {
     // ===== MMA issuers: each warp stays converged; one elected lane issues tcgen05.mma / commit =====
     const int me = warp == 1 ? 0 : 1;  // which of the alternating slabs this warp takes
@@ -309,23 +458,37 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     const uint32_t a_lo_fixed = (uint32_t)(kPlaneBytes >> 4) << 16;  // LBO = one 8-channel plane
     if (SPLIT) {
       // this warp drives board `me` only; every slab passes through both issuers and is released by the second commit
-      const uint32_t my_acc = me == 0 ? bar_acc : bar_acc1, my_act = me == 0 ? bar_act : bar_act1;
-      const uint32_t tmem_d = tmem_base + (uint32_t)me * 128;
+      const uint32_t my_acc = me == 0 ? bar_acc : bar_acc1, my_act = me == 0 ? bar_act : bar_act1, my_hi = me == 0 ? bar_hi0 : bar_hi1;
+      const uint32_t tmem_board = tmem_base + (uint32_t)me * ((PP && !(p.debug & 1024u)) ? 256 : 128);
+      uint32_t acc_sel = 0;  // MODE 4: which of the board's two accumulators this layer fills
       for (int64_t lead = lead0; lead < n_pairs && ok; lead += gridDim.x) {
         for (int l = 0; l < p.n_layers && ok; ++l) {
           const TowerLayer& L = p.layers[l];
           ok = __all_sync(0xffffffffu, wait_bar(my_act, act_phase, p.status, 2u));
           if (!ok) break;
-          act_phase ^= 1;
+          const int half = PP ? L.half_slab : 0;
+          const uint32_t tmem_d = tmem_board + acc_sel * 128u;
+          if (PP && half == 0) {
+            ok = __all_sync(0xffffffffu, wait_bar(my_hi, act_phase, p.status, 2u));
+            if (!ok) break;
+          }
           tc_fence_after();
           const uint32_t idesc = idesc_bf16(kM, (uint32_t)L.cout);
           const uint32_t b_lbo16 = (uint32_t)L.cout, b_lo_fixed = b_lbo16 << 16;
           const int mma_per_slab = L.ks / 16;
           const uint32_t a_img16 = (act_u + (uint32_t)(me * 2 + L.src) * kBufBytes) >> 4;
           for (int s = 0; s < L.n_slabs; ++s) {
+            if (PP && s == half && half > 0) {  // the rest of the ring order reads channels >= 64
+              ok = __all_sync(0xffffffffu, wait_bar(my_hi, act_phase, p.status, 2u));
+              if (!ok) break;
+              tc_fence_after();
+            }
             const uint32_t a16 = a_img16 + L.aoff[s];
-            ok = __all_sync(0xffffffffu, wait_bar(bar_full + 8 * stage, phase, p.status, 4u));
-            if (!ok) break;
+            if (!(p.debug & 8192u)) {  // 8192: timing experiment without the weight ring (issue loop + MMAs only)
+              ok = __all_sync(0xffffffffu, (p.debug & 4096u) ? wait_bar_spin(bar_full + 8 * stage, phase, p.status, 4u)
+                                                             : wait_bar(bar_full + 8 * stage, phase, p.status, 4u));
+              if (!ok) break;
+            }
             tc_fence_after();
             const uint32_t b16 = (ring_u + stage * SB) >> 4;
             if (elect_one()) {
@@ -334,13 +497,16 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
                 else if (mma_per_slab == 2) issue_slab1<2>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
                 else issue_slab1<1>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
               }
-              mma_commit(bar_empty + 8 * stage);
+              if (!(p.debug & 8192u)) mma_commit(bar_empty + 8 * stage);
             }
             __syncwarp();
             if (++stage == NS) { stage = 0; phase ^= 1; }
           }
+          if (PP && ok && half >= L.n_slabs) ok = __all_sync(0xffffffffu, wait_bar(my_hi, act_phase, p.status, 2u));  // keep the phases paired
+          act_phase ^= 1;
           if (ok && elect_one()) mma_commit(my_acc);
           __syncwarp();
+          if (PP && !(p.debug & 512u)) acc_sel ^= 1u;  // the next layer accumulates into the board's other accumulator
         }
       }
     } else if (PAIR && me != 0) {
@@ -422,24 +588,32 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     const uint32_t keep = inside ? 0xFFFFFFFFu : 0u;
     const int pos = y * p.cols + x;  // compact position index (token order h*W + w)
     const uint32_t my_act_u = act_u + (uint32_t)eb * 2 * kBufBytes + (uint32_t)(kHalo + m) * 16;  // this row, plane 0, buffer 0
-    const uint32_t tmem_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)eb * 128;
-    uint32_t acc_phase = 0;
+    const uint32_t tmem_row0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)eb * ((PP && !(p.debug & 1024u)) ? 256 : 128);
+    uint32_t acc_phase = 0, acc_sel = 0;
     bool ok = true;
     // "this layer's image is written": in pair mode every epilogue warp of both CTAs reports to the leader's barrier
     const uint32_t act_target = PAIR && rank != 0 ? mapa_smem(bar_act, 0) : bar_act;
     const uint32_t my_act = SPLIT && eb == 1 ? bar_act1 : bar_act;
     const uint32_t my_acc = SPLIT && eb == 1 ? bar_acc1 : bar_acc;
-    auto arrive_act = [&]() {
+    const uint32_t my_hi = eb == 1 ? bar_hi1 : bar_hi0;
+    auto arrive_on = [&](uint32_t bar) {
       fence_proxy_async_smem();
       __syncwarp();
       if (lane == 0) {
         if (PAIR && rank != 0) mbar_arrive_remote(act_target);
-        else mbar_arrive(my_act);
+        else mbar_arrive(bar);
       }
+    };
+    auto arrive_act = [&]() {
+      arrive_on(my_act);
+      if (PP) arrive_on(my_hi);
     };
     for (int64_t lead = lead0, pair = pair0; lead < n_pairs && ok; lead += gridDim.x, pair += gridDim.x) {
       const int64_t board = pair * kBoards + eb;
       const bool valid = board < p.batch;
+      // The previous board's last epilogue may still be reading its residual from image 0 in the sibling warp (other
+      // channel share, same rows): all eight epilogue warps of this board finish it before anyone writes the new image.
+      if (!(p.debug & 2048u)) asm volatile("bar.sync %0, %1;" ::"r"(1 + eb), "r"(kEpiWarps / kBoards * 32) : "memory");
       // ---- layer 0 on CUDA cores, straight from the bitmasks (extractor.py:33-46 + conv_body.0) ----
       if (!(p.debug & 8u)) {
         float g[9];
@@ -487,8 +661,16 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         uint8_t* gdst = p.fc_a + (((board >> 7) * p.n_kc + (int64_t)pos * (L.cout / 8)) * 128 + (board & 127)) * 16;
         const bool gstore = valid && inside;
         const int cout = (p.debug & 4u) ? 0 : L.cout;
+        const uint32_t tmem_row = tmem_row0 + acc_sel * 128u;
+        if (PP && !(p.debug & 512u)) acc_sel ^= 1u;
+        const bool more = l + 1 < p.n_layers;
+        bool lo_sent = false;
 #pragma unroll 1
         for (int c0 = eh * 32; c0 < cout; c0 += 32 * kEpiSplit) {
+          if (PP && more && c0 >= 64 && !lo_sent) {  // channels 0-63 of the new image are in place: the next layer may start
+            arrive_on(my_act);
+            lo_sent = true;
+          }
           uint32_t r[32];
           tmem_ld32(tmem_row + (uint32_t)c0, r);
           tmem_ld_wait();
@@ -510,7 +692,14 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
           }
         }
         tc_fence_before();  // TMEM reads are done before the next layer's MMAs overwrite the accumulator
-        if (l + 1 < p.n_layers) arrive_act();
+        if (more) {
+          if (PP) {
+            if (!lo_sent) arrive_on(my_act);
+            arrive_on(my_hi);
+          } else {
+            arrive_act();
+          }
+        }
       }
     }
   }
@@ -521,7 +710,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     cluster_sync_all();  // neither CTA frees tensor memory or exits while its peer may still touch it
     if (warp == 0) tmem_dealloc2(tmem_base, kBoards * 128);
   } else {
-    if (warp == 0) tmem_dealloc(tmem_base, kBoards * 128);
+    if (warp == 0) tmem_dealloc(tmem_base, PP ? 2 * kBoards * 128 : kBoards * 128);
   }
 }
 
@@ -790,6 +979,8 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
       const int shift = L.taps == 9 ? (tap / 3 - 1) * kPadW + (tap % 3 - 1) : 0;
       L.aoff[sl] = (uint32_t)((ch0 / 8) * kPlaneBytes + (kHalo + shift) * 16) >> 4;
     }
+    for (int sl = 0; sl < kMaxSlabs; ++sl) L.slab_src[sl] = (uint8_t)sl;
+    L.half_slab = 0;
     L.src = src; L.dst = dst; L.res = res; L.act = c.f.act; L.bias_slot = slot;
     b->layer_wt.push_back(c.f.wt);
     b->layer_k.push_back(c.f.K);
@@ -905,7 +1096,10 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
   AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
   AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
   AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
-  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
+  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
+  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
+  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
     AT_TOWER_ATTR(AT_ACT_RELU)
     AT_TOWER_ATTR(AT_ACT_GELU)
     AT_TOWER_ATTR(AT_ACT_SILU)
@@ -1055,6 +1249,25 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
         }
       }
     }
+    if ((mode == 4 || mode == 6) && !(tp.debug & 256u)) {
+      // ring order: the slabs that read input channels < 64 first (stable), see TowerLayer::slab_src
+      for (int l = 0; l < tp.n_layers; ++l) {
+        TowerLayer& L = tp.layers[l];
+        const int planes_lo = (64 / 8) * kPlaneBytes;  // image offset of channel 64
+        uint32_t nat[kMaxSlabs];
+        for (int sl = 0; sl < L.n_slabs; ++sl) nat[sl] = L.aoff[sl];
+        auto is_hi = [&](int sl) {
+          const int k0 = sl * L.ks;
+          return (k0 % L.cin) * kPlaneBytes / 8 >= planes_lo;
+        };
+        int n = 0;
+        for (int sl = 0; sl < L.n_slabs; ++sl)
+          if (!is_hi(sl)) { L.slab_src[n] = (uint8_t)sl; L.aoff[n] = nat[sl]; ++n; }
+        L.half_slab = n;
+        for (int sl = 0; sl < L.n_slabs; ++sl)
+          if (is_hi(sl)) { L.slab_src[n] = (uint8_t)sl; L.aoff[n] = nat[sl]; ++n; }
+      }
+    }
     cudaLaunchConfig_t cfg{};
     cudaLaunchAttribute attr[1];
     cfg.blockDim = dim3(kTowerThreads);
@@ -1079,6 +1292,9 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
   if (pair) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 1>, tp));               \
   else if (mode == 2) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 2>, tp));     \
   else if (mode == 3) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 3>, tp));     \
+  else if (mode == 4) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 4>, tp));     \
+  else if (mode == 5) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 5>, tp));     \
+  else if (mode == 6) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 6>, tp));     \
   else AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 0>, tp));
     switch (tp.act0) {
       case AT_ACT_RELU: AT_TOWER_LAUNCH(AT_ACT_RELU) break;

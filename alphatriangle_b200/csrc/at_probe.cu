@@ -173,6 +173,133 @@ __global__ void __launch_bounds__(128, 1) probe_ts_kernel(const ProbeTsArgs p) {
   if (warp == 0) tmem_dealloc(tmem_base, 512);
 }
 
+// ---- throughput probe -----------------------------------------------------------------------------------------
+// How fast does one SM retire M=128 x N x K=16 bf16 MMAs with both operands in shared memory (the convolution tower's
+// shape), and what do concurrent bulk copies into shared memory / tensor-memory reads by other warps cost? Every CTA of
+// the grid runs the same loop so the chip is in its loaded clock / power state; out[cta] = cycles per MMA seen by issuer 0.
+struct RateArgs {
+  int n, mmas, issuers, copy, epi_warps;
+  const uint8_t* src;  // >= 32 KB of readable global memory (bulk-copy source)
+  float* out;
+};
+
+constexpr int kRateThreads = 32 * 20;
+constexpr uint32_t kRateImage = 37392, kRateRing = 4 * 16384, kRateCopy = 2 * 16384, kRateScratch = 16 * 1024;
+
+__global__ void __launch_bounds__(kRateThreads, 1) mma_rate_kernel(const RateArgs p) {
+  extern __shared__ __align__(1024) uint8_t smem[];
+  __shared__ __align__(8) uint64_t bars[6];
+  __shared__ uint32_t tmem_base_s;
+  __shared__ volatile int done_s;
+  const int tid = threadIdx.x, warp = tid / 32, lane = tid % 32;
+  const uint32_t ring_u = smem_u32(smem), img_u = ring_u + kRateRing, copy_u = img_u + ((kRateImage + 1023u) & ~1023u);
+  const uint32_t scratch_u = copy_u + kRateCopy;
+  for (uint32_t i = tid; i < (scratch_u + kRateScratch - ring_u) / 16; i += kRateThreads) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0, 0, 0, 0);
+  if (tid == 0) {
+    for (int i = 0; i < 6; ++i) mbar_init(smem_u32(&bars[i]), 1);
+    fence_mbar_init();
+    done_s = 0;
+  }
+  if (warp == 0) {
+    tmem_alloc(smem_u32(&tmem_base_s), 512);
+    tmem_relinquish();
+  }
+  fence_proxy_async_smem();
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = tmem_base_s;
+
+  if (p.copy >= 10) {
+    // latency variants (out[cta] = cycles per round): 10 / 11 = mbarrier ping-pong between two warps (try_wait / test_wait),
+    // 12 = tcgen05.commit -> mbarrier with an empty pipe, 13 = one MMA + commit -> mbarrier (issue-to-completion latency)
+    const uint32_t b0 = smem_u32(&bars[0]), b1 = smem_u32(&bars[1]);
+    const int rounds = p.mmas;
+    if (lane == 0 && warp == 0) {
+      const uint32_t idesc = idesc_bf16(128, (uint32_t)p.n);
+      constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
+      const uint64_t da = ((uint64_t)kDescHi << 32) | ((2320u >> 4) << 16) | ((img_u + 17 * 16) >> 4);
+      const uint64_t db = ((uint64_t)kDescHi << 32) | (((uint32_t)p.n) << 16) | (ring_u >> 4);
+      const long long t0 = clock64();
+      for (int i = 0; i < rounds; ++i) {
+        const uint32_t ph = (uint32_t)i & 1u;
+        if (p.copy == 10 || p.copy == 11) {
+          mbar_arrive(b0);
+          if (p.copy == 10) { while (!mbar_try_wait(b1, ph)) {} } else { while (!mbar_test_wait(b1, ph)) {} }
+        } else {
+          if (p.copy == 13) mma_bf16(tmem_base, da, db, idesc, false);
+          mma_commit(b0);
+          while (!mbar_test_wait(b0, ph)) {}
+        }
+      }
+      p.out[blockIdx.x] = (float)(clock64() - t0) / (float)rounds;
+    } else if (lane == 0 && warp == 1 && (p.copy == 10 || p.copy == 11)) {
+      for (int i = 0; i < rounds; ++i) {
+        const uint32_t ph = (uint32_t)i & 1u;
+        if (p.copy == 10) { while (!mbar_try_wait(b0, ph)) {} } else { while (!mbar_test_wait(b0, ph)) {} }
+        mbar_arrive(b1);
+      }
+    }
+  } else if (warp < 2) {
+    if (warp < p.issuers && lane == 0) {
+      const uint32_t idesc = idesc_bf16(128, (uint32_t)p.n);
+      const uint32_t tmem_d = tmem_base + (uint32_t)warp * 256;
+      const uint32_t bar = smem_u32(&bars[warp]);
+      constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
+      const uint32_t a_fixed = (2320u >> 4) << 16, b_fixed = ((uint32_t)p.n) << 16;  // LBO: A one plane, B n rows of 16 bytes
+      const long long t0 = clock64();
+      for (int i = 0; i < p.mmas; ++i) {
+        const int tap = (i >> 2) % 9, j = i & 3;
+        const uint32_t a16 = (img_u + (uint32_t)((17 + (tap / 3 - 1) * 16 + (tap % 3 - 1)) * 16) + (uint32_t)j * 2 * 2320u) >> 4;
+        const uint32_t b16 = (ring_u + (uint32_t)((i >> 2) & 3) * 16384u + (uint32_t)j * 2 * (uint32_t)p.n * 16u) >> 4;
+        mma_bf16(tmem_d, ((uint64_t)kDescHi << 32) | a_fixed | a16, ((uint64_t)kDescHi << 32) | b_fixed | b16, idesc, i > 0);
+      }
+      mma_commit(bar);
+      mbar_wait(bar, 0);
+      const long long t1 = clock64();
+      if (warp == 0) {
+        p.out[blockIdx.x] = (float)(t1 - t0) / (float)p.mmas;
+        done_s = 1;
+      }
+    }
+  } else if (warp == 2) {
+    if (lane == 0 && p.copy) {  // back-to-back 16 KB bulk copies, two in flight, for as long as the issuer runs
+      uint32_t ph[2] = {0, 0};
+      int i = 0;
+      for (; !done_s; ++i) {
+        const int b = i & 1;
+        const uint32_t bar = smem_u32(&bars[2 + b]);
+        if (i >= 2) {
+          mbar_wait(bar, ph[b]);
+          ph[b] ^= 1;
+        }
+        mbar_arrive_expect_tx(bar, 16384);
+        bulk_g2s(copy_u + b * 16384, p.src + b * 16384, 16384, bar);
+      }
+      for (int b = 0; b < 2 && b < i; ++b) mbar_wait(smem_u32(&bars[2 + b]), ph[b]);  // nothing may land after the CTA is gone
+    }
+  } else if (warp - 3 < p.epi_warps) {
+    // epilogue-like traffic: tensor-memory reads of this warp's lane quarter + 128-bit shared stores / loads
+    const uint32_t trow = tmem_base + ((uint32_t)((warp % 4) * 32) << 16) + (uint32_t)(((warp - 3) / 4) % 4) * 32;
+    const uint32_t my = scratch_u + (uint32_t)(tid % 512) * 16;
+    uint32_t sink = 0;
+    while (!done_s) {
+      uint32_t r[32];
+      tmem_ld32(trow, r);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(my + (uint32_t)(i & 1) * 8192u), "r"(r[i * 8]), "r"(r[i * 8 + 1]), "r"(r[i * 8 + 2]), "r"(r[i * 8 + 3]) : "memory");
+        sink += r[i * 8 + 4];
+      }
+    }
+    if (sink == 0x12345678u) p.out[0] = 0.0f;
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) tmem_dealloc(tmem_base, 512);
+}
+
 }  // namespace
 
 }  // namespace at
@@ -209,6 +336,20 @@ extern "C" int at_probe_umma(const void* d_a_image, int64_t a_bytes, const void*
               n, k, a_start_off, a_lbo, a_sbo, a_kstep, b_start_off, b_lbo, b_sbo, b_kstep, (uint32_t)layout_type, d_out, d_status};
   AT_CUDA_TRY(cudaFuncSetAttribute(probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   probe_kernel<<<1, 128, smem, static_cast<cudaStream_t>(stream)>>>(p);
+  AT_CUDA_TRY(cudaGetLastError());
+  return AT_OK;
+}
+
+extern "C" int at_probe_mma_rate(int n, int mmas, int issuers, int copy, int epi_warps, const void* d_src, int grid, float* d_cycles,
+                                 void* stream) {
+  using namespace at;
+  if (!d_src || !d_cycles) return fail(AT_E_INVALID, "at_probe_mma_rate: null pointer");
+  if (n < 16 || n > 256 || n % 16 != 0 || mmas < 1 || issuers < 1 || issuers > 2 || epi_warps < 0 || epi_warps > 16 || grid < 1)
+    return fail(AT_E_INVALID, "at_probe_mma_rate: bad argument");
+  RateArgs p{n, mmas, issuers, copy, epi_warps, static_cast<const uint8_t*>(d_src), d_cycles};
+  const size_t smem = kRateRing + ((kRateImage + 1023u) & ~1023u) + kRateCopy + kRateScratch + 1024;
+  AT_CUDA_TRY(cudaFuncSetAttribute(mma_rate_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  mma_rate_kernel<<<grid, kRateThreads, smem, static_cast<cudaStream_t>(stream)>>>(p);
   AT_CUDA_TRY(cudaGetLastError());
   return AT_OK;
 }

@@ -199,6 +199,13 @@ int at_probe_umma_ts(const void* d_a_rows, const void* d_b_image, int64_t b_byte
                      uint32_t a_cols_per_kstep, uint32_t b_start_off, uint32_t b_lbo, uint32_t b_sbo, uint32_t b_kstep, float* d_out,
                      uint32_t* d_status, void* stream);
 
+/* Throughput probe: every CTA of `grid` issues `mmas` back-to-back 128 x n x 16 bf16 MMAs (operands in shared memory, the
+ * tower's layout) from `issuers` (1 or 2) warps, optionally while another warp streams 16 KB bulk copies into shared
+ * memory (`copy` != 0) and `epi_warps` warps read tensor memory / store to shared memory like the tower's epilogue.
+ * d_cycles[cta] = SM cycles per MMA of issuer 0. No reference counterpart: measures the hardware ceiling DESIGN.md quotes. */
+int at_probe_mma_rate(int n, int mmas, int issuers, int copy, int epi_warps, const void* d_src /* >= 32 KB */, int grid,
+                      float* d_cycles /* [grid] */, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
