@@ -50,12 +50,9 @@ constexpr int kMaxSlabs = 36;                // weight slabs per layer (9 taps x
 constexpr int kBoards = 2;                   // boards in flight per CTA
 constexpr int kEpiSplit = 2;                 // epilogue warps per (board, TMEM lane quarter): each takes 1/kEpiSplit of the channels
 constexpr int kEpiWarps = kBoards * 4 * kEpiSplit;
-constexpr int kMmaWarpB = 2 + kEpiWarps;      // second MMA-issuing warp (odd slabs); warp 1 takes the even ones
-constexpr int kTowerThreads = 64 + kEpiWarps * 32 + 32 + 64;  // + two more issuing warps (MODE 5 / 6)
-constexpr int kMaxBars = 40;                 // mbarrier slots reserved in shared memory
-// CTA-pair mode (cta_group::2): each CTA streams half of every weight slab, so stages are half as big and twice as many
-constexpr int kStages2 = 8;
-constexpr int kStageBytes2 = 8192;
+constexpr int kMmaWarpB = 2 + kEpiWarps;      // MMA-issuing warp of board 1; warp 1 issues for board 0
+constexpr int kTowerThreads = 64 + kEpiWarps * 32 + 32;
+constexpr int kMaxBars = 32;                 // mbarrier slots reserved in shared memory
 constexpr long long kTimeoutCycles = 2000000000LL;  // ~1 s: a wedged pipeline reports instead of hanging
 
 struct TowerLayer {
@@ -67,11 +64,6 @@ struct TowerLayer {
   // where each weight slab's first MMA reads its A operand, relative to the source image, >> 4: the slab covers channels
   // [c0, c0 + ks) of one tap, i.e. plane c0/8 of the image shifted by (dy*16 + dx) rows
   uint32_t aoff[kMaxSlabs];
-  // MODE 4: ring order. Slab s of the ring is slab slab_src[s] of the packed stream (aoff is already in ring order): the slabs
-  // that read input channels < 64 come first, so they can run while the producer layer's epilogue still writes channels >= 64.
-  // half_slab = first ring slab that needs channels >= 64 (n_slabs if none does).
-  uint8_t slab_src[kMaxSlabs];
-  int half_slab;
 };
 
 struct TowerParams {
@@ -88,7 +80,7 @@ struct TowerParams {
   int n_kc;                // L * C_last / 8
   int rows, cols;
   uint32_t* status;
-  uint32_t debug;  // timing experiments only (AT_TOWER_DEBUG): 1 no weight copies, 2 no MMAs, 4 no epilogue math, 8 no layer 0
+  uint32_t debug;  // timing experiments only (AT_TOWER_DEBUG): 1 no weight copies, 2 no MMAs, 4 no epilogue math, 8 no layer 0, 16 no weight ring
 };
 
 constexpr size_t tower_smem_bytes() {
@@ -106,34 +98,6 @@ __device__ __forceinline__ bool wait_bar(uint32_t bar, uint32_t parity, uint32_t
   if (mbar_try_wait(bar, parity)) return true;  // common case: no clock reads on the fast path
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > kTimeoutCycles) {
-      atomicOr(status, code);
-      return false;
-    }
-  }
-  return true;
-}
-
-// Busy-polling flavour for the warps on the per-slab critical path (weight producer, MMA issuers): test_wait never parks
-// the thread, so the wake-up after the phase flips costs one poll instead of the hardware's suspend granularity.
-__device__ __forceinline__ bool wait_bar_spin(uint32_t bar, uint32_t parity, uint32_t* status, uint32_t code) {
-  for (int i = 0; i < 64; ++i)
-    if (mbar_test_wait(bar, parity)) return true;
-  const long long t0 = clock64();
-  while (!mbar_test_wait(bar, parity)) {
-    if (clock64() - t0 > kTimeoutCycles) {
-      atomicOr(status, code);
-      return false;
-    }
-  }
-  return true;
-}
-
-// same, for a barrier the peer CTA of the pair arrives on (cluster-scope acquire)
-__device__ __forceinline__ bool wait_bar_cluster(uint32_t bar, uint32_t parity, uint32_t* status, uint32_t code) {
-  if (mbar_try_wait_cluster(bar, parity)) return true;
-  const long long t0 = clock64();
-  while (!mbar_try_wait_cluster(bar, parity)) {
     if (clock64() - t0 > kTimeoutCycles) {
       atomicOr(status, code);
       return false;
@@ -181,35 +145,14 @@ __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   return v;
 }
 
-// One weight slab against both boards' images: NM K-steps of 16 channels each, A advancing two 8-channel planes per
-// step, B advancing two planes of the slab. Descriptor high words are constant (SBO = 128 B, version 1, no swizzle).
-template <int NM, bool PAIR = false>
-__device__ __forceinline__ void issue_slab(uint32_t tmem_base, uint32_t a0_16, uint32_t a1_16, uint32_t b16, uint32_t a_lo_fixed,
-                                           uint32_t b_lo_fixed, uint32_t b_step16, uint32_t idesc, bool first,
-                                           uint32_t tmem_board_stride = 128) {
-  constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
-#pragma unroll
-  for (int b = 0; b < kBoards; ++b) {
-    const uint32_t a16 = b == 0 ? a0_16 : a1_16;
-#pragma unroll
-    for (int j = 0; j < NM; ++j) {
-      const uint32_t a_lo = a_lo_fixed | (a16 + (uint32_t)j * (2 * kPlaneBytes >> 4));
-      const uint32_t b_lo = b_lo_fixed | (b16 + (uint32_t)j * b_step16);
-      if constexpr (PAIR)
-        mma_bf16_2cta(tmem_base + (uint32_t)b * tmem_board_stride, ((uint64_t)kDescHi << 32) | a_lo, ((uint64_t)kDescHi << 32) | b_lo, idesc,
-                      !(first && j == 0));
-      else
-        mma_bf16(tmem_base + (uint32_t)b * tmem_board_stride, ((uint64_t)kDescHi << 32) | a_lo, ((uint64_t)kDescHi << 32) | b_lo, idesc,
-                 !(first && j == 0));
-    }
-  }
-}
+// Descriptor high words are constant: SBO = 128 B (rows of a core matrix 16 B apart), version 1, no swizzle.
+constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
 
-// one board only (board-independent pipelines, MODE 3)
+// NM K-steps of one weight slab against one board's image (used by the fused tower + transformer kernel): A advances two
+// 8-channel planes per step, B two planes of the slab.
 template <int NM>
 __device__ __forceinline__ void issue_slab1(uint32_t tmem_d, uint32_t a16, uint32_t b16, uint32_t a_lo_fixed, uint32_t b_lo_fixed,
                                             uint32_t b_step16, uint32_t idesc, bool first) {
-  constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
 #pragma unroll
   for (int j = 0; j < NM; ++j) {
     const uint32_t a_lo = a_lo_fixed | (a16 + (uint32_t)j * (2 * kPlaneBytes >> 4));
@@ -218,33 +161,34 @@ __device__ __forceinline__ void issue_slab1(uint32_t tmem_d, uint32_t a16, uint3
   }
 }
 
-// ACT = the model-wide activation (every conv_block and ResidualBlock of a model shares it, model.py:127)
-// PAIR = two CTAs of a cluster drive one tensor-core pair (tcgen05 cta_group::2): every MMA covers board b of BOTH CTAs
-// (M = 256) and each CTA keeps only its half of the weight slab (N/2 rows of B), which halves the shared-memory reads
-// of B per SM and the L2 -> SM weight traffic. Rank 0 issues; rank 1's MMA warp only relays "my half has landed".
-// MODE 0: one CTA per SM, 4 ring stages of 16 KB (64 K-values per slab); MODE 1: CTA pairs, 8 stages of 8 KB (each CTA's half of
-// a 64-K slab); MODE 2: one CTA per SM, 8 stages of 8 KB (32 K-values per slab) -- twice as many slabs in flight.
-// MODE 3: like 0, but the two boards of a CTA are INDEPENDENT pipelines that only share the weight ring: one issuing warp and
-// eight epilogue warps per board, each board with its own accumulator / image-ready barriers. While one board's epilogue
-// drains its accumulator (tensor memory reads run at ~64 B/clock), the other board's MMAs keep the tensor pipe busy.
-// MODE 4: MODE 3 + overlap inside a board. Both boards walk the shared weight ring within four slabs of each other, so their
-// epilogues coincide and the tensor pipe idles meanwhile. Here every board has TWO accumulators (layers alternate) and the
-// "image written" signal is split by channel half: the epilogue reports channels 0-63 after its first pass, and the next
-// layer -- whose slabs are streamed lower-channel-half first -- starts accumulating into the other accumulator while the
-// second pass (channels 64-127) is still draining tensor memory. Half of every epilogue disappears under MMAs.
-// MODE 5: MODE 3 with TWO issuing warps per board taking alternate slabs: the ~90 instructions of per-slab bookkeeping (barrier
-// wait, descriptor arithmetic, commit) are a dependent chain of ~450 cycles in one warp -- as long as the four MMAs it
-// feeds -- and the issue itself blocks while the pipe is busy; with a sibling warp the bookkeeping of slab s+1 runs under
-// the MMAs of slab s. MODE 6 = 5 + 4.
-template <int ACT, int MODE>
+// The convolution tower: one CTA per SM, two boards per CTA, persistent over board pairs.
+//
+//   warp 0            weight producer: one thread streams the pair's slab sequence through a 4 x 16 KB ring (bulk copies
+//                     global -> shared, completion on the stage's "full" mbarrier)
+//   warp 1, warp 18   MMA issuers, one per board (converged warp, one elected lane): per layer wait for the board's input image, then per
+//                     slab wait "full", issue the slab's K-steps (tcgen05.mma, M=128 positions x N=Cout x K=16) into the
+//                     board's accumulator, commit to the stage's "empty" barrier (two commits, one per board, free a
+//                     stage); after the last slab commit to the board's "accumulator complete" barrier
+//   warps 2..17       epilogue, 8 per board (4 TMEM lane quarters x 2 channel shares): layer 0 on CUDA cores from the
+//                     bitmasks, then per layer tcgen05.ld -> +bias (+residual) -> activation -> bf16 -> next image
+//
+// The two boards are independent pipelines that share only the weight ring: while one board's epilogue drains its
+// accumulator (tensor-memory reads run at ~64 B/clock) the other board's MMAs can keep the tensor pipe busy.
+//
+// What was measured on the way here (profiles/r01_tower_*.txt, r01_mma_rate_probe.txt):
+//  * two issuing threads on different accumulators saturate the pipe at 64 cycles per 128x128x16 MMA, also while bulk copies
+//    and epilogue traffic hit shared memory; one thread alone reaches 85;
+//  * a tcgen05.mma holds its issuing thread while the pipe is busy, so an issuer's per-slab time is its bookkeeping PLUS the
+//    256 cycles of its four MMAs: the bookkeeping has to stay well under 256 cycles for the pipe to fill. Hence one plain
+//    thread per board with a short loop (no votes, elections or warp syncs per slab), and the next slab's operand offset
+//    fetched while the current one is issued;
+//  * tried and dropped: CTA pairs with cta_group::2, an 8 x 8 KB ring, two issuing warps per board (no gain, and the
+//    accumulation order -- hence the low bits -- then depends on timing), two accumulators per board with a channel-half
+//    hand-off (overlap gain smaller than the added per-slab instructions).
+template <int ACT>
 __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_constant__ TowerParams p) {
-  constexpr bool PAIR = MODE == 1;
-  constexpr bool SPLIT = MODE >= 3;
-  constexpr bool PP = MODE == 4 || MODE == 6;  // two accumulators per board + channel-half hand-off (see the comment above)
-  constexpr bool QUAD = MODE >= 5;             // two issuing warps per board, alternate slabs (see the comment above)
-  constexpr int NS = (MODE == 1 || MODE == 2) ? kStages2 : kStages;               // ring stages
-  constexpr uint32_t SB = (MODE == 1 || MODE == 2) ? kStageBytes2 : kStageBytes;  // bytes per stage
-  static_assert(NS * SB == kStages * kStageBytes, "both modes use the same ring footprint");
+  constexpr int NS = kStages;
+  constexpr uint32_t SB = kStageBytes;
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* ring = smem;
   uint8_t* act = ring + kStages * kStageBytes;                        // [board][buf][kBufBytes]
@@ -255,20 +199,11 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kMaxBars);
 
   const int tid = threadIdx.x, warp = tid / 32, lane = tid % 32;
-  const uint32_t rank = PAIR ? cluster_ctarank() : 0u;
   const uint32_t ring_u = smem_u32(ring), act_u = smem_u32(act);
-  const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + NS), bar_full2 = smem_u32(bars + 2 * NS);
-  const uint32_t bar_acc = smem_u32(bars + 3 * NS), bar_act = smem_u32(bars + 3 * NS + 1), bar_first = smem_u32(bars + 3 * NS + 2);
-  // Two warps issue MMAs, taking alternate weight slabs: issuing a tcgen05.mma holds the issuing warp until the tensor pipe
-  // accepts it, so a single issuer cannot overlap its per-slab bookkeeping (barrier wait, descriptors, commit: ~400 cycles)
-  // with the 512 cycles its 8 MMAs run -- measured additive. With two issuers one warp's bookkeeping hides under the other's MMAs.
-  constexpr int kIssuers = PAIR ? 1 : 2;
-  // MODE 3 barriers of board 1 (board 0 uses bar_acc / bar_act)
-  const uint32_t bar_acc1 = smem_u32(bars + 3 * NS + 3), bar_act1 = smem_u32(bars + 3 * NS + 4);
-  // MODE 4: "channels >= 64 of the image are written", per board (bar_act / bar_act1 then mean channels < 64)
-  const uint32_t bar_hi0 = smem_u32(bars + 3 * NS + 5), bar_hi1 = smem_u32(bars + 3 * NS + 6);
-  // MODE 5/6: "the layer's first (overwriting) MMA of this board is in the pipe", per board
-  const uint32_t bar_first0 = smem_u32(bars + 3 * NS + 7), bar_first1 = smem_u32(bars + 3 * NS + 8);
+  const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + NS);
+  const uint32_t bar_acc0 = smem_u32(bars + 2 * NS), bar_acc1 = smem_u32(bars + 2 * NS + 1);  // accumulator of board b complete
+  const uint32_t bar_act0 = smem_u32(bars + 2 * NS + 2), bar_act1 = smem_u32(bars + 2 * NS + 3);  // input image of board b written
+  const bool use_ring = !(p.debug & 16u);  // 16: timing experiment without the weight ring (issue loop + MMAs + epilogue only)
 
   // ---- one-time setup --------------------------------------------------------------------
   for (int i = tid; i < kBoards * 2 * kBufBytes / 16; i += kTowerThreads) reinterpret_cast<uint4*>(act)[i] = make_uint4(0, 0, 0, 0);
@@ -278,307 +213,111 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   if (tid == 0) {
     for (int i = 0; i < NS; ++i) {
       mbar_init(bar_full + 8 * i, 1);
-      mbar_init(bar_empty + 8 * i, SPLIT ? 2 : 1);  // MODE 3: both boards' issuers are done with the slab
-      mbar_init(bar_full2 + 8 * i, 1);
+      mbar_init(bar_empty + 8 * i, kBoards);  // both boards' issuers are done with the slab
     }
-    mbar_init(bar_acc, QUAD ? 2 : (SPLIT ? 1 : kIssuers));  // every issuing warp commits its share of the layer
-    mbar_init(bar_first, 1);
-    mbar_init(bar_act, PAIR ? 2 * kEpiWarps : (SPLIT ? kEpiWarps / 2 : kEpiWarps));  // one arrival per epilogue warp
-    mbar_init(bar_acc1, QUAD ? 2 : 1);
-    mbar_init(bar_first0, 1);
-    mbar_init(bar_first1, 1);
-    mbar_init(bar_act1, kEpiWarps / 2);
-    mbar_init(bar_hi0, kEpiWarps / 2);
-    mbar_init(bar_hi1, kEpiWarps / 2);
+    mbar_init(bar_acc0, 1);
+    mbar_init(bar_acc1, 1);
+    mbar_init(bar_act0, kEpiWarps / kBoards);  // one arrival per epilogue warp of the board
+    mbar_init(bar_act1, kEpiWarps / kBoards);
     fence_mbar_init();
   }
   if (warp == 0) {
-    if constexpr (PAIR) {
-      tmem_alloc2(smem_u32(tmem_slot), kBoards * 128);
-      tmem_relinquish2();
-    } else {
-      tmem_alloc(smem_u32(tmem_slot), PP ? 2 * kBoards * 128 : kBoards * 128);
-      tmem_relinquish();
-    }
+    tmem_alloc(smem_u32(tmem_slot), kBoards * 128);
+    tmem_relinquish();
   }
   fence_proxy_async_smem();  // the zeroed halos are read by the tensor core (async proxy)
   tc_fence_before();
   __syncthreads();
-  if constexpr (PAIR) cluster_sync_all();  // the peer's barriers exist before anyone arrives on them remotely
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
   const int64_t n_pairs = (p.batch + kBoards - 1) / kBoards;
-  // this CTA's first board pair; both CTAs of a cluster run the same number of rounds (the second may idle on the tail)
   const int64_t pair0 = blockIdx.x;
-  const int64_t lead0 = PAIR ? (int64_t)(blockIdx.x & ~1u) : (int64_t)blockIdx.x;
 
-  if (QUAD && warp == 0) {
-    // ===== weight producer, MODE 5/6: lane i owns ring stage i and streams slabs i, i+NS, ... of the pair's slab sequence.
-    // The per-slab chain (barrier wait, expect_tx, bulk copy: ~400 cycles of dependent long-latency operations in one thread)
-    // then runs for NS slabs at once. =====
-    if (lane < NS) {
-      int l = 0, s = lane;
-      int64_t lead = lead0;
-      uint32_t base = 0, phase = 0;
-      auto settle = [&]() {  // carry the cursor over layer / board-pair ends
-        while (lead < n_pairs && s >= p.layers[l].n_slabs) {
-          s -= p.layers[l].n_slabs;
-          base += (uint32_t)p.layers[l].n_slabs * p.layers[l].slab_bytes;
-          if (++l == p.n_layers) {
-            l = 0;
-            base = 0;
-            lead += gridDim.x;
-          }
-        }
-      };
-      settle();
-      const uint32_t my_full = bar_full + 8 * lane, my_empty = bar_empty + 8 * lane, my_ring = ring_u + lane * SB;
-      while (lead < n_pairs) {
-        const TowerLayer& L = p.layers[l];
-        if (!wait_bar(my_empty, phase ^ 1, p.status, 1u)) break;
-        if (p.debug & 1u) {
-          mbar_arrive(my_full);
-        } else {
-          const uint32_t bytes = L.slab_bytes;
-          mbar_arrive_expect_tx(my_full, bytes);
-          bulk_g2s(my_ring, p.wstream + base + (uint32_t)(PP ? (int)L.slab_src[s] : s) * bytes, bytes, my_full);
-        }
-        phase ^= 1;
-        s += NS;
-        settle();
-      }
-    }
-  } else if (warp == 0) {
-    // ===== weight producer: one lane streams every layer's slabs through the ring =====
-    if (lane == 0 && !(p.debug & 8192u)) {
-      int stage = 0;
-      uint32_t phase = 0;
+  if (warp == 0) {
+    // ===== weight producer: one thread streams every layer's slabs through the ring, refilling each stage as soon as it
+    // is released (a lane-per-stage variant refills in lock step -- all four lanes leave their waits together -- and was
+    // measured slower) =====
+    if (lane == 0 && use_ring) {
+      uint32_t stage = 0, phase = 0;
       bool ok = true;
-      for (int64_t lead = lead0; lead < n_pairs && ok; lead += gridDim.x) {
+      for (int64_t pair = pair0; pair < n_pairs && ok; pair += gridDim.x) {
         const uint8_t* src = p.wstream;
         for (int l = 0; l < p.n_layers && ok; ++l) {
-          const uint32_t slab = p.layers[l].slab_bytes;
-          const uint32_t bytes = PAIR ? slab / 2 : slab;  // pair mode: this CTA's N/2 rows, stored as [slab][half]
-          for (int s = 0; s < p.layers[l].n_slabs; ++s) {
-            ok = (p.debug & 4096u) ? wait_bar_spin(bar_empty + 8 * stage, phase ^ 1, p.status, 1u)
-                                   : wait_bar(bar_empty + 8 * stage, phase ^ 1, p.status, 1u);
+          const uint32_t bytes = p.layers[l].slab_bytes;
+          const int n_slabs = p.layers[l].n_slabs;
+          for (int s = 0; s < n_slabs; ++s) {
+            ok = wait_bar(bar_empty + 8 * stage, phase ^ 1, p.status, 1u);
             if (!ok) break;
             if (p.debug & 1u) {
               mbar_arrive(bar_full + 8 * stage);
             } else {
               mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
-              const uint8_t* from = PP ? src + ((int)p.layers[l].slab_src[s] - s) * (int64_t)slab : src + (PAIR ? rank * bytes : 0u);
-              bulk_g2s(ring_u + stage * SB, from, bytes, bar_full + 8 * stage);
+              bulk_g2s(ring_u + stage * SB, src, bytes, bar_full + 8 * stage);
             }
-            src += slab;
-            if (++stage == NS) { stage = 0; phase ^= 1; }
+            src += bytes;
+            stage = (stage + 1) & (NS - 1);
+            phase ^= (stage == 0);
           }
         }
       }
     }
-  } else if (QUAD && (warp == 1 || warp >= kMmaWarpB)) {
-    // ===== MODE 5/6 issuers: warp (board me, parity par) takes the board's slabs par, par+2, ... of every layer. One thread
-    // runs the whole loop: nothing here needs the other lanes, and votes / elections per slab only lengthen the chain. =====
-    const int wi = warp == 1 ? 0 : warp - kMmaWarpB + 1;
-    const int me = wi & 1, par = wi >> 1;
-    if (lane == 0) {
-      const uint32_t my_acc = me == 0 ? bar_acc : bar_acc1, my_act = me == 0 ? bar_act : bar_act1, my_hi = me == 0 ? bar_hi0 : bar_hi1;
-      const uint32_t my_first = me == 0 ? bar_first0 : bar_first1;
-      const uint32_t tmem_board = tmem_base + (uint32_t)me * (PP ? 256 : 128);
-      const uint32_t a_lo_fixed = (uint32_t)(kPlaneBytes >> 4) << 16;  // LBO = one 8-channel plane
-      const bool no_mma = (p.debug & 2u) != 0;
-      uint32_t g = 0;       // ring slabs this board has passed (every issuer counts all of them)
-      uint32_t lphase = 0;  // parity of the per-layer barriers
-      uint32_t acc_sel = 0;
-      bool ok = true;
-      for (int64_t lead = lead0; lead < n_pairs && ok; lead += gridDim.x) {
-        for (int l = 0; l < p.n_layers && ok; ++l) {
-          const TowerLayer& L = p.layers[l];
-          const int n_slabs = L.n_slabs;
-          const int half = PP ? L.half_slab : 0;
-          ok = wait_bar(my_act, lphase, p.status, 2u);
-          if (!ok) break;
-          bool hi_seen = !PP;
-          if (PP && half == 0) {
-            ok = wait_bar(my_hi, lphase, p.status, 2u);
-            if (!ok) break;
-            hi_seen = true;
-          }
-          if (par == 1) {  // never accumulate onto the previous layer's sums: slab 0 (accumulate off) goes first
-            ok = wait_bar(my_first, lphase, p.status, 2u);
-            if (!ok) break;
-          }
-          tc_fence_after();
-          const uint32_t tmem_d = tmem_board + acc_sel * 128u;
-          const uint32_t idesc = idesc_bf16(kM, (uint32_t)L.cout);
-          const uint32_t b_lbo16 = (uint32_t)L.cout, b_lo_fixed = b_lbo16 << 16;
-          const int mma_per_slab = no_mma ? 0 : L.ks / 16;
-          const uint32_t a_img16 = (act_u + (uint32_t)(me * 2 + L.src) * kBufBytes) >> 4;
-          uint32_t a_next = par < n_slabs ? L.aoff[par] : 0u;
-          for (int s = par; s < n_slabs; s += 2) {
-            if (PP && !hi_seen && s >= half) {
-              ok = wait_bar(my_hi, lphase, p.status, 2u);
-              if (!ok) break;
-              hi_seen = true;
-            }
-            const uint32_t gs = g + (uint32_t)s, stage = gs % NS, ph = (gs / NS) & 1u;
-            const uint32_t a16 = a_img16 + a_next;
-            if (s + 2 < n_slabs) a_next = L.aoff[s + 2];  // the next slab's offset is in flight while this one is issued
-            ok = wait_bar(bar_full + 8 * stage, ph, p.status, 4u);
-            if (!ok) break;
-            tc_fence_after();
-            const uint32_t b16 = (ring_u + stage * SB) >> 4;
-            if (mma_per_slab == 4) issue_slab1<4>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
-            else if (mma_per_slab == 2) issue_slab1<2>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
-            else if (mma_per_slab == 1) issue_slab1<1>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
-            mma_commit(bar_empty + 8 * stage);
-            if (s == 0) mbar_arrive(my_first);
-          }
-          if (!ok) break;
-          if (PP && !hi_seen) {  // keep the barrier phases paired
-            ok = wait_bar(my_hi, lphase, p.status, 2u);
-            if (!ok) break;
-          }
-          mma_commit(my_acc);
-          g += (uint32_t)n_slabs;
-          lphase ^= 1u;
-          if (PP) acc_sel ^= 1u;
-        }
-      }
-    }
-  } else if (warp > kMmaWarpB) {
-    // the extra issuing warps idle in the other modes
   } else if (warp == 1 || warp == kMmaWarpB) {
-    // ===== MMA issuers: each warp stays converged; one elected lane issues tcgen05.mma / commit =====
-    const int me = warp == 1 ? 0 : 1;  // which of the alternating slabs this warp takes
-    int stage = 0;
-    uint32_t phase = 0, act_phase = 0, first_phase = 0;
-    bool ok = true;
+    // ===== MMA issuer of board `me`: the warp stays converged, one elected lane issues tcgen05.mma / commit =====
+    // (Measured against a single-thread loop under one elect.sync: that one has fewer instructions per slab -- its
+    // skeleton without MMAs runs 20 % faster -- but the full kernel is 1.5 % slower with it.)
+    const int me = warp == 1 ? 0 : 1;
+    const uint32_t my_acc = me == 0 ? bar_acc0 : bar_acc1, my_act = me == 0 ? bar_act0 : bar_act1;
+    const uint32_t tmem_d = tmem_base + (uint32_t)me * 128;
     const uint32_t a_lo_fixed = (uint32_t)(kPlaneBytes >> 4) << 16;  // LBO = one 8-channel plane
-    if (SPLIT) {
-      // this warp drives board `me` only; every slab passes through both issuers and is released by the second commit
-      const uint32_t my_acc = me == 0 ? bar_acc : bar_acc1, my_act = me == 0 ? bar_act : bar_act1, my_hi = me == 0 ? bar_hi0 : bar_hi1;
-      const uint32_t tmem_board = tmem_base + (uint32_t)me * ((PP && !(p.debug & 1024u)) ? 256 : 128);
-      uint32_t acc_sel = 0;  // MODE 4: which of the board's two accumulators this layer fills
-      for (int64_t lead = lead0; lead < n_pairs && ok; lead += gridDim.x) {
-        for (int l = 0; l < p.n_layers && ok; ++l) {
-          const TowerLayer& L = p.layers[l];
-          ok = __all_sync(0xffffffffu, wait_bar(my_act, act_phase, p.status, 2u));
-          if (!ok) break;
-          const int half = PP ? L.half_slab : 0;
-          const uint32_t tmem_d = tmem_board + acc_sel * 128u;
-          if (PP && half == 0) {
-            ok = __all_sync(0xffffffffu, wait_bar(my_hi, act_phase, p.status, 2u));
+    const bool no_mma = (p.debug & 2u) != 0;
+    uint32_t stage = 0, phase = 0, lphase = 0;
+    bool ok = true;
+    for (int64_t pair = pair0; pair < n_pairs && ok; pair += gridDim.x) {
+      for (int l = 0; l < p.n_layers && ok; ++l) {
+        const TowerLayer& L = p.layers[l];
+        ok = __all_sync(0xffffffffu, wait_bar(my_act, lphase, p.status, 2u));  // this layer's input image is written
+        if (!ok) break;
+        lphase ^= 1u;
+        tc_fence_after();
+        const uint32_t idesc = idesc_bf16(kM, (uint32_t)L.cout);
+        // descriptor low words: [13:0] start address >> 4, [29:16] LBO >> 4; the address sums below stay inside 14 bits
+        const uint32_t a_base = a_lo_fixed | ((act_u + (uint32_t)(me * 2 + L.src) * kBufBytes) >> 4);
+        const uint32_t b_base = ((uint32_t)L.cout << 16) | (ring_u >> 4);  // LBO = one 8-channel plane of the slab (Cout rows of 16 B)
+        const uint32_t b_step = 2u * (uint32_t)L.cout;                      // one K-step = two planes
+        const int n_slabs = L.n_slabs;
+        const int steps = no_mma ? 0 : L.ks / 16;
+        for (int s = 0; s < n_slabs; ++s) {
+          const uint32_t a_lo = a_base + L.aoff[s];
+          if (use_ring) {
+            ok = __all_sync(0xffffffffu, wait_bar(bar_full + 8 * stage, phase, p.status, 4u));
             if (!ok) break;
           }
           tc_fence_after();
-          const uint32_t idesc = idesc_bf16(kM, (uint32_t)L.cout);
-          const uint32_t b_lbo16 = (uint32_t)L.cout, b_lo_fixed = b_lbo16 << 16;
-          const int mma_per_slab = L.ks / 16;
-          const uint32_t a_img16 = (act_u + (uint32_t)(me * 2 + L.src) * kBufBytes) >> 4;
-          for (int s = 0; s < L.n_slabs; ++s) {
-            if (PP && s == half && half > 0) {  // the rest of the ring order reads channels >= 64
-              ok = __all_sync(0xffffffffu, wait_bar(my_hi, act_phase, p.status, 2u));
-              if (!ok) break;
-              tc_fence_after();
+          const uint32_t b_lo = b_base + stage * (SB >> 4);
+          if (elect_one()) {
+            if (steps == 4) {
+#pragma unroll
+              for (int j = 0; j < 4; ++j)
+                mma_bf16(tmem_d, ((uint64_t)kDescHi << 32) | (a_lo + (uint32_t)j * (2 * kPlaneBytes >> 4)),
+                         ((uint64_t)kDescHi << 32) | (b_lo + (uint32_t)j * b_step), idesc, s > 0 || j > 0);
+            } else {
+              for (int j = 0; j < steps; ++j)
+                mma_bf16(tmem_d, ((uint64_t)kDescHi << 32) | (a_lo + (uint32_t)j * (2 * kPlaneBytes >> 4)),
+                         ((uint64_t)kDescHi << 32) | (b_lo + (uint32_t)j * b_step), idesc, s > 0 || j > 0);
             }
-            const uint32_t a16 = a_img16 + L.aoff[s];
-            if (!(p.debug & 8192u)) {  // 8192: timing experiment without the weight ring (issue loop + MMAs only)
-              ok = __all_sync(0xffffffffu, (p.debug & 4096u) ? wait_bar_spin(bar_full + 8 * stage, phase, p.status, 4u)
-                                                             : wait_bar(bar_full + 8 * stage, phase, p.status, 4u));
-              if (!ok) break;
-            }
-            tc_fence_after();
-            const uint32_t b16 = (ring_u + stage * SB) >> 4;
-            if (elect_one()) {
-              if (!(p.debug & 2u)) {
-                if (mma_per_slab == 4) issue_slab1<4>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
-                else if (mma_per_slab == 2) issue_slab1<2>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
-                else issue_slab1<1>(tmem_d, a16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
-              }
-              if (!(p.debug & 8192u)) mma_commit(bar_empty + 8 * stage);
-            }
-            __syncwarp();
-            if (++stage == NS) { stage = 0; phase ^= 1; }
-          }
-          if (PP && ok && half >= L.n_slabs) ok = __all_sync(0xffffffffu, wait_bar(my_hi, act_phase, p.status, 2u));  // keep the phases paired
-          act_phase ^= 1;
-          if (ok && elect_one()) mma_commit(my_acc);
-          __syncwarp();
-          if (PP && !(p.debug & 512u)) acc_sel ^= 1u;  // the next layer accumulates into the board's other accumulator
-        }
-      }
-    } else if (PAIR && me != 0) {
-      // pair mode keeps a single issuer
-    } else if (PAIR && rank != 0) {
-      // rank 1 of a pair issues nothing: it tells the leader when its half of each slab has landed
-      for (int64_t lead = lead0; lead < n_pairs && ok; lead += gridDim.x)
-        for (int l = 0; l < p.n_layers && ok; ++l)
-          for (int s = 0; s < p.layers[l].n_slabs; ++s) {
-            ok = __all_sync(0xffffffffu, wait_bar(bar_full + 8 * stage, phase, p.status, 4u));
-            if (!ok) break;
-            if (lane == 0) mbar_arrive_remote(mapa_smem(bar_full2 + 8 * stage, 0));
-            __syncwarp();
-            if (++stage == NS) { stage = 0; phase ^= 1; }
-          }
-    } else {
-      for (int64_t lead = lead0; lead < n_pairs && ok; lead += gridDim.x) {
-        for (int l = 0; l < p.n_layers && ok; ++l) {
-          const TowerLayer& L = p.layers[l];
-          // this layer's input images are written (in pair mode: in both CTAs)
-          ok = __all_sync(0xffffffffu, PAIR ? wait_bar_cluster(bar_act, act_phase, p.status, 2u) : wait_bar(bar_act, act_phase, p.status, 2u));
-          if (!ok) break;
-          act_phase ^= 1;
-          tc_fence_after();
-          const uint32_t idesc = idesc_bf16(PAIR ? 2 * kM : kM, (uint32_t)L.cout);
-          const uint32_t b_lbo16 = PAIR ? (uint32_t)L.cout / 2 : (uint32_t)L.cout;  // 8-channel plane of this CTA's B rows, >> 4
-          const uint32_t b_lo_fixed = b_lbo16 << 16;
-          const int mma_per_slab = L.ks / 16;
-          const int n_slabs = L.n_slabs;
-          const uint32_t a0_img16 = (act_u + (uint32_t)(0 * 2 + L.src) * kBufBytes) >> 4;
-          const uint32_t a1_img16 = (act_u + (uint32_t)(1 * 2 + L.src) * kBufBytes) >> 4;
-          for (int s = 0; s < n_slabs; ++s) {
-            if (kIssuers == 2 && (s & 1) != me) {  // the other warp's slab: just keep the ring position in step
-              if (++stage == NS) { stage = 0; phase ^= 1; }
-              continue;
-            }
-            const uint32_t a_off16 = L.aoff[s];
-            ok = __all_sync(0xffffffffu, wait_bar(bar_full + 8 * stage, phase, p.status, 4u));
-            if (ok && PAIR) ok = __all_sync(0xffffffffu, wait_bar_cluster(bar_full2 + 8 * stage, phase, p.status, 32u));
-            // slab 0 carries the MMAs that overwrite (rather than accumulate into) the accumulators: nobody issues before it
-            if (ok && kIssuers == 2 && me == 1 && s == 1) ok = __all_sync(0xffffffffu, wait_bar(bar_first, first_phase, p.status, 64u));
-            if (!ok) break;
-            tc_fence_after();
-            const uint32_t b16 = (ring_u + stage * SB) >> 4;
-            if (elect_one()) {
-              if (!(p.debug & 2u)) {
-                if (mma_per_slab == 4)
-                  issue_slab<4, PAIR>(tmem_base, a0_img16 + a_off16, a1_img16 + a_off16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
-                else if (mma_per_slab == 2)
-                  issue_slab<2, PAIR>(tmem_base, a0_img16 + a_off16, a1_img16 + a_off16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
-                else
-                  issue_slab<1, PAIR>(tmem_base, a0_img16 + a_off16, a1_img16 + a_off16, b16, a_lo_fixed, b_lo_fixed, 2 * b_lbo16, idesc, s == 0);
-              }
-              // the slab may be overwritten (in both CTAs) once these MMAs retire
-              if constexpr (PAIR) mma_commit_2cta(bar_empty + 8 * stage, 3);
-              else mma_commit(bar_empty + 8 * stage);
-              if (kIssuers == 2 && s == 0) mbar_arrive(bar_first);  // the overwriting MMAs are in the pipe
-            }
-            __syncwarp();
-            if (++stage == NS) { stage = 0; phase ^= 1; }
-          }
-          first_phase ^= 1;
-          if (ok && elect_one()) {  // every board's accumulator of this layer is complete
-            if constexpr (PAIR) mma_commit_2cta(bar_acc, 3);
-            else mma_commit(bar_acc);
+            if (use_ring) mma_commit(bar_empty + 8 * stage);  // the slab may be overwritten once these MMAs retire
           }
           __syncwarp();
+          stage = (stage + 1) & (NS - 1);
+          phase ^= (stage == 0);
         }
+        if (ok && elect_one()) mma_commit(my_acc);
+        __syncwarp();
       }
     }
   } else {
-    // ===== epilogue warps: 4 per board; warp%4 selects the TMEM lane quarter =====
+    // ===== epilogue warps: 8 per board; warp%4 selects the TMEM lane quarter =====
     const int eb = (warp - 2) / (4 * kEpiSplit);   // board of the pair
     const int eh = ((warp - 2) / 4) % kEpiSplit;   // which share of the channels
     const int q = warp % 4;                        // TMEM lane quarter this warp may read
@@ -588,32 +327,22 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     const uint32_t keep = inside ? 0xFFFFFFFFu : 0u;
     const int pos = y * p.cols + x;  // compact position index (token order h*W + w)
     const uint32_t my_act_u = act_u + (uint32_t)eb * 2 * kBufBytes + (uint32_t)(kHalo + m) * 16;  // this row, plane 0, buffer 0
-    const uint32_t tmem_row0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)eb * ((PP && !(p.debug & 1024u)) ? 256 : 128);
-    uint32_t acc_phase = 0, acc_sel = 0;
+    const uint32_t tmem_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)eb * 128;
+    uint32_t acc_phase = 0;
     bool ok = true;
-    // "this layer's image is written": in pair mode every epilogue warp of both CTAs reports to the leader's barrier
-    const uint32_t act_target = PAIR && rank != 0 ? mapa_smem(bar_act, 0) : bar_act;
-    const uint32_t my_act = SPLIT && eb == 1 ? bar_act1 : bar_act;
-    const uint32_t my_acc = SPLIT && eb == 1 ? bar_acc1 : bar_acc;
-    const uint32_t my_hi = eb == 1 ? bar_hi1 : bar_hi0;
-    auto arrive_on = [&](uint32_t bar) {
+    const uint32_t my_act = eb == 1 ? bar_act1 : bar_act0;
+    const uint32_t my_acc = eb == 1 ? bar_acc1 : bar_acc0;
+    auto arrive_act = [&]() {
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) {
-        if (PAIR && rank != 0) mbar_arrive_remote(act_target);
-        else mbar_arrive(bar);
-      }
+      if (lane == 0) mbar_arrive(my_act);
     };
-    auto arrive_act = [&]() {
-      arrive_on(my_act);
-      if (PP) arrive_on(my_hi);
-    };
-    for (int64_t lead = lead0, pair = pair0; lead < n_pairs && ok; lead += gridDim.x, pair += gridDim.x) {
+    for (int64_t pair = pair0; pair < n_pairs && ok; pair += gridDim.x) {
       const int64_t board = pair * kBoards + eb;
       const bool valid = board < p.batch;
       // The previous board's last epilogue may still be reading its residual from image 0 in the sibling warp (other
       // channel share, same rows): all eight epilogue warps of this board finish it before anyone writes the new image.
-      if (!(p.debug & 2048u)) asm volatile("bar.sync %0, %1;" ::"r"(1 + eb), "r"(kEpiWarps / kBoards * 32) : "memory");
+      if (!(p.debug & 64u)) asm volatile("bar.sync %0, %1;" ::"r"(1 + eb), "r"(kEpiWarps / kBoards * 32) : "memory");
       // ---- layer 0 on CUDA cores, straight from the bitmasks (extractor.py:33-46 + conv_body.0) ----
       if (!(p.debug & 8u)) {
         float g[9];
@@ -661,16 +390,8 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         uint8_t* gdst = p.fc_a + (((board >> 7) * p.n_kc + (int64_t)pos * (L.cout / 8)) * 128 + (board & 127)) * 16;
         const bool gstore = valid && inside;
         const int cout = (p.debug & 4u) ? 0 : L.cout;
-        const uint32_t tmem_row = tmem_row0 + acc_sel * 128u;
-        if (PP && !(p.debug & 512u)) acc_sel ^= 1u;
-        const bool more = l + 1 < p.n_layers;
-        bool lo_sent = false;
 #pragma unroll 1
         for (int c0 = eh * 32; c0 < cout; c0 += 32 * kEpiSplit) {
-          if (PP && more && c0 >= 64 && !lo_sent) {  // channels 0-63 of the new image are in place: the next layer may start
-            arrive_on(my_act);
-            lo_sent = true;
-          }
           uint32_t r[32];
           tmem_ld32(tmem_row + (uint32_t)c0, r);
           tmem_ld_wait();
@@ -692,26 +413,14 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
           }
         }
         tc_fence_before();  // TMEM reads are done before the next layer's MMAs overwrite the accumulator
-        if (more) {
-          if (PP) {
-            if (!lo_sent) arrive_on(my_act);
-            arrive_on(my_hi);
-          } else {
-            arrive_act();
-          }
-        }
+        if (l + 1 < p.n_layers) arrive_act();
       }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if constexpr (PAIR) {
-    cluster_sync_all();  // neither CTA frees tensor memory or exits while its peer may still touch it
-    if (warp == 0) tmem_dealloc2(tmem_base, kBoards * 128);
-  } else {
-    if (warp == 0) tmem_dealloc(tmem_base, PP ? 2 * kBoards * 128 : kBoards * 128);
-  }
+  if (warp == 0) tmem_dealloc(tmem_base, kBoards * 128);
 }
 
 // ---- trunk FC: split-K tcgen05 GEMM ---------------------------------------------------------
@@ -837,23 +546,6 @@ __global__ void __launch_bounds__(256) pack_b_kernel(const float* __restrict__ w
   }
 }
 
-// same weights for CTA-pair mode: every slab of `ks` K-values is stored as two halves, [slab][half][ks/8][N/2][8], so that
-// each CTA of a pair bulk-copies just the N/2 rows of B it feeds to the shared MMA
-__global__ void __launch_bounds__(256) pack_b_split_kernel(const float* __restrict__ wt, int K, int N, int ks, __nv_bfloat16* __restrict__ dst) {
-  const int64_t total = (int64_t)K * N;
-  const int hn = N / 2;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int e = (int)(i % 8);
-    int64_t t = i / 8;
-    const int row = (int)(t % hn); t /= hn;
-    const int plane = (int)(t % (ks / 8)); t /= (ks / 8);
-    const int half = (int)(t % 2);
-    const int slab = (int)(t / 2);
-    const int k = slab * ks + plane * 8 + e, n = half * hn + row;
-    dst[i] = __float2bfloat16_rn(wt[(int64_t)k * N + n]);
-  }
-}
-
 __global__ void gather_bias_kernel(const float* __restrict__ folded, const int64_t* __restrict__ offs, const int* __restrict__ widths,
                                    int n_layers, float* __restrict__ dst) {
   const int l = blockIdx.x;
@@ -882,9 +574,6 @@ struct Bf16Path {
   size_t wstream_bytes = 0;
   // per weight set
   uint8_t* wstream[2] = {nullptr, nullptr};
-  uint8_t* wstream_pair[2] = {nullptr, nullptr};  // the same slabs split in halves for CTA-pair mode
-  std::vector<int> layer_ks;
-  bool pair_mode = false;
   uint8_t* wfc[2] = {nullptr, nullptr};
   float* bias[2] = {nullptr, nullptr};
   int64_t* d_bias_off = nullptr;
@@ -979,12 +668,9 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
       const int shift = L.taps == 9 ? (tap / 3 - 1) * kPadW + (tap % 3 - 1) : 0;
       L.aoff[sl] = (uint32_t)((ch0 / 8) * kPlaneBytes + (kHalo + shift) * 16) >> 4;
     }
-    for (int sl = 0; sl < kMaxSlabs; ++sl) L.slab_src[sl] = (uint8_t)sl;
-    L.half_slab = 0;
     L.src = src; L.dst = dst; L.res = res; L.act = c.f.act; L.bias_slot = slot;
     b->layer_wt.push_back(c.f.wt);
     b->layer_k.push_back(c.f.K);
-    b->layer_ks.push_back(L.ks);
     b->bias_off.push_back(c.f.bias);
     b->bias_w.push_back(c.cout);
     b->wstream_bytes += (size_t)c.f.K * c.cout * 2;
@@ -1072,7 +758,6 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
   auto alloc = [&]() -> int {
     for (int i = 0; i < 2; ++i) {
       AT_CUDA_TRY(cudaMalloc(&b->wstream[i], b->wstream_bytes));
-      if (!b->tf) AT_CUDA_TRY(cudaMalloc(&b->wstream_pair[i], b->conv_stream_bytes));
       AT_CUDA_TRY(cudaMalloc(&b->wfc[i], (size_t)p.flat * fc.N * 2));
       AT_CUDA_TRY(cudaMalloc(&b->bias[i], (size_t)kMaxLayers * 128 * sizeof(float)));
     }
@@ -1092,14 +777,8 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
     AT_CUDA_TRY(cudaMalloc(&b->status, 4 * sizeof(uint32_t)));
     AT_CUDA_TRY(cudaMemset(b->status, 0, 4 * sizeof(uint32_t)));
     for (auto& e : b->ev) AT_CUDA_TRY(cudaEventCreate(&e));
-#define AT_TOWER_ATTR(ACT_)                                                                                                     \
-  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
-  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
-  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
-  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
-  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
-  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 5>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
-  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+#define AT_TOWER_ATTR(ACT_) \
+  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
     AT_TOWER_ATTR(AT_ACT_RELU)
     AT_TOWER_ATTR(AT_ACT_GELU)
     AT_TOWER_ATTR(AT_ACT_SILU)
@@ -1122,7 +801,6 @@ void bf16_destroy(Bf16Path* b) {
   if (!b) return;
   for (int i = 0; i < 2; ++i) {
     cudaFree(b->wstream[i]);
-    cudaFree(b->wstream_pair[i]);
     cudaFree(b->wfc[i]);
     cudaFree(b->bias[i]);
     cudaFree(b->tfp[i]);
@@ -1145,11 +823,6 @@ int bf16_pack_weights(Bf16Path* b, const Plan& p, const float* folded, int slot,
     const int K = b->layer_k[l], N = b->bias_w[l];
     pack_b_kernel<<<148, 256, 0, st>>>(folded + b->layer_wt[l], K, N, reinterpret_cast<__nv_bfloat16*>(b->wstream[slot] + off));
     AT_CUDA_TRY(cudaGetLastError());
-    if (b->wstream_pair[slot]) {
-      pack_b_split_kernel<<<148, 256, 0, st>>>(folded + b->layer_wt[l], K, N, b->layer_ks[l],
-                                               reinterpret_cast<__nv_bfloat16*>(b->wstream_pair[slot] + off));
-      AT_CUDA_TRY(cudaGetLastError());
-    }
     off += (size_t)K * N * 2;
   }
   pack_b_kernel<<<148 * 4, 256, 0, st>>>(folded + b->fc_wt, b->fc_flat, b->fc_n, reinterpret_cast<__nv_bfloat16*>(b->wfc[slot]));
@@ -1227,84 +900,14 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
     t.pe = folded + p.pe;
     if (tp.act0 == AT_ACT_RELU) tower_tf_kernel<AT_ACT_RELU><<<grid, kTfThreads, tower_tf_smem_bytes(), st>>>(t);
     else tower_tf_kernel<AT_ACT_GELU><<<grid, kTfThreads, tower_tf_smem_bytes(), st>>>(t);
-  } else
-  {
-    // CTA-pair mode (tcgen05 cta_group::2) unless AT_TOWER_PAIR=0: clusters of two CTAs, an even grid
-    const char* pm = getenv("AT_TOWER_MODE");
-    const int mode = pm ? atoi(pm) : 3;  // default: board-independent pipelines (see tower_kernel); 0/1/2 kept for experiments
-    const bool pair = mode == 1 && b->wstream_pair[slot] != nullptr && b->sms >= 2;
-    if (mode == 2) {
-      // same weight stream (chunk-major [K/8][N][8]); only the slab granularity changes: 32 K-values per slab
-      for (int l = 0; l < tp.n_layers; ++l) {
-        TowerLayer& L = tp.layers[l];
-        if (L.ks <= 32) continue;
-        L.ks = 32;
-        L.n_slabs = L.taps * L.cin / 32;
-        L.slab_bytes = 32u * (uint32_t)L.cout * 2u;
-        for (int sl = 0; sl < L.n_slabs && sl < kMaxSlabs; ++sl) {
-          const int k0 = sl * 32;
-          const int tap = k0 / L.cin, ch0 = k0 - tap * L.cin;
-          const int shift = L.taps == 9 ? (tap / 3 - 1) * kPadW + (tap % 3 - 1) : 0;
-          L.aoff[sl] = (uint32_t)((ch0 / 8) * kPlaneBytes + (kHalo + shift) * 16) >> 4;
-        }
-      }
-    }
-    if ((mode == 4 || mode == 6) && !(tp.debug & 256u)) {
-      // ring order: the slabs that read input channels < 64 first (stable), see TowerLayer::slab_src
-      for (int l = 0; l < tp.n_layers; ++l) {
-        TowerLayer& L = tp.layers[l];
-        const int planes_lo = (64 / 8) * kPlaneBytes;  // image offset of channel 64
-        uint32_t nat[kMaxSlabs];
-        for (int sl = 0; sl < L.n_slabs; ++sl) nat[sl] = L.aoff[sl];
-        auto is_hi = [&](int sl) {
-          const int k0 = sl * L.ks;
-          return (k0 % L.cin) * kPlaneBytes / 8 >= planes_lo;
-        };
-        int n = 0;
-        for (int sl = 0; sl < L.n_slabs; ++sl)
-          if (!is_hi(sl)) { L.slab_src[n] = (uint8_t)sl; L.aoff[n] = nat[sl]; ++n; }
-        L.half_slab = n;
-        for (int sl = 0; sl < L.n_slabs; ++sl)
-          if (is_hi(sl)) { L.slab_src[n] = (uint8_t)sl; L.aoff[n] = nat[sl]; ++n; }
-      }
-    }
-    cudaLaunchConfig_t cfg{};
-    cudaLaunchAttribute attr[1];
-    cfg.blockDim = dim3(kTowerThreads);
-    cfg.dynamicSmemBytes = tower_smem_bytes();
-    cfg.stream = st;
-    if (pair) {
-      tp.wstream = b->wstream_pair[slot];
-      unsigned g2 = (unsigned)(((n_pairs + 1) / 2) * 2);
-      const unsigned cap = (unsigned)(b->sms & ~1);
-      if (g2 > cap) g2 = cap;
-      cfg.gridDim = dim3(g2);
-      attr[0].id = cudaLaunchAttributeClusterDimension;
-      attr[0].val.clusterDim.x = 2;
-      attr[0].val.clusterDim.y = 1;
-      attr[0].val.clusterDim.z = 1;
-      cfg.attrs = attr;
-      cfg.numAttrs = 1;
-    } else {
-      cfg.gridDim = dim3(grid);
-    }
-#define AT_TOWER_LAUNCH(ACT_)                                                               \
-  if (pair) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 1>, tp));               \
-  else if (mode == 2) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 2>, tp));     \
-  else if (mode == 3) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 3>, tp));     \
-  else if (mode == 4) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 4>, tp));     \
-  else if (mode == 5) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 5>, tp));     \
-  else if (mode == 6) AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 6>, tp));     \
-  else AT_CUDA_TRY(cudaLaunchKernelEx(&cfg, tower_kernel<ACT_, 0>, tp));
+  } else {
     switch (tp.act0) {
-      case AT_ACT_RELU: AT_TOWER_LAUNCH(AT_ACT_RELU) break;
-      case AT_ACT_GELU: AT_TOWER_LAUNCH(AT_ACT_GELU) break;
-      case AT_ACT_SILU: AT_TOWER_LAUNCH(AT_ACT_SILU) break;
-      case AT_ACT_TANH: AT_TOWER_LAUNCH(AT_ACT_TANH) break;
-      default: AT_TOWER_LAUNCH(AT_ACT_SIGMOID) break;
+      case AT_ACT_RELU: tower_kernel<AT_ACT_RELU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
+      case AT_ACT_GELU: tower_kernel<AT_ACT_GELU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
+      case AT_ACT_SILU: tower_kernel<AT_ACT_SILU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
+      case AT_ACT_TANH: tower_kernel<AT_ACT_TANH><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
+      default: tower_kernel<AT_ACT_SIGMOID><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
     }
-#undef AT_TOWER_LAUNCH
-    b->pair_mode = pair;
   }
   AT_CUDA_TRY(cudaGetLastError());
   AT_CUDA_TRY(cudaEventRecord(b->ev[1], st));

@@ -184,7 +184,7 @@ struct RateArgs {
 };
 
 constexpr int kRateThreads = 32 * 20;
-constexpr uint32_t kRateImage = 37392, kRateRing = 4 * 16384, kRateCopy = 2 * 16384, kRateScratch = 16 * 1024;
+constexpr uint32_t kRateImage = 2 * 38912, kRateRing = 4 * 16384, kRateCopy = 2 * 16384, kRateScratch = 16 * 1024;  // one image per issuer
 
 __global__ void __launch_bounds__(kRateThreads, 1) mma_rate_kernel(const RateArgs p) {
   extern __shared__ __align__(1024) uint8_t smem[];
@@ -210,7 +210,7 @@ __global__ void __launch_bounds__(kRateThreads, 1) mma_rate_kernel(const RateArg
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
 
-  if (p.copy >= 10) {
+  if (p.copy >= 10 && p.copy < 20) {
     // latency variants (out[cta] = cycles per round): 10 / 11 = mbarrier ping-pong between two warps (try_wait / test_wait),
     // 12 = tcgen05.commit -> mbarrier with an empty pipe, 13 = one MMA + commit -> mbarrier (issue-to-completion latency)
     const uint32_t b0 = smem_u32(&bars[0]), b1 = smem_u32(&bars[1]);
@@ -248,9 +248,26 @@ __global__ void __launch_bounds__(kRateThreads, 1) mma_rate_kernel(const RateArg
       constexpr uint32_t kDescHi = (128u >> 4) | (1u << 14);
       const uint32_t a_fixed = (2320u >> 4) << 16, b_fixed = ((uint32_t)p.n) << 16;  // LBO: A one plane, B n rows of 16 bytes
       const long long t0 = clock64();
+      if (p.copy >= 32) {
+        // the tower's per-slab pattern: copy = 32 + flags; per four MMAs: 1 = mbarrier try_wait (on a phase that is already
+        // complete), 2 = tcgen05.commit to a barrier nobody waits on, 4 = tcgen05.fence::after_thread_sync
+        const bool f_wait = p.copy & 1, f_commit = p.copy & 2, f_fence = p.copy & 4;
+        const uint32_t bw = smem_u32(&bars[5]), bc = smem_u32(&bars[4]) ;
+        const uint32_t a_base = a_fixed | ((img_u + (uint32_t)warp * 38912u + 17u * 16u) >> 4), b_base = b_fixed | (ring_u >> 4);
+        for (int sl = 0; sl < p.mmas / 4; ++sl) {
+          if (f_wait) { while (!mbar_try_wait(bw, 1)) {} }
+          if (f_fence) tc_fence_after();
+          const uint32_t a_lo = a_base + (uint32_t)(sl & 7), b_lo = b_base + (uint32_t)(sl & 3) * 1024u;
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            mma_bf16(tmem_d, ((uint64_t)kDescHi << 32) | (a_lo + (uint32_t)j * 290u), ((uint64_t)kDescHi << 32) | (b_lo + (uint32_t)j * 256u), idesc,
+                     sl > 0 || j > 0);
+          if (f_commit) mma_commit(bc);
+        }
+      } else
       for (int i = 0; i < p.mmas; ++i) {
         const int tap = (i >> 2) % 9, j = i & 3;
-        const uint32_t a16 = (img_u + (uint32_t)((17 + (tap / 3 - 1) * 16 + (tap % 3 - 1)) * 16) + (uint32_t)j * 2 * 2320u) >> 4;
+        const uint32_t a16 = (img_u + (uint32_t)warp * 38912u + (uint32_t)((17 + (tap / 3 - 1) * 16 + (tap % 3 - 1)) * 16) + (uint32_t)j * 2 * 2320u) >> 4;
         const uint32_t b16 = (ring_u + (uint32_t)((i >> 2) & 3) * 16384u + (uint32_t)j * 2 * (uint32_t)p.n * 16u) >> 4;
         mma_bf16(tmem_d, ((uint64_t)kDescHi << 32) | a_fixed | a16, ((uint64_t)kDescHi << 32) | b_fixed | b16, idesc, i > 0);
       }
@@ -263,7 +280,7 @@ __global__ void __launch_bounds__(kRateThreads, 1) mma_rate_kernel(const RateArg
       }
     }
   } else if (warp == 2) {
-    if (lane == 0 && p.copy) {  // back-to-back 16 KB bulk copies, two in flight, for as long as the issuer runs
+    if (lane == 0 && p.copy && p.copy < 10) {  // back-to-back 16 KB bulk copies, two in flight, for as long as the issuer runs
       uint32_t ph[2] = {0, 0};
       int i = 0;
       for (; !done_s; ++i) {
@@ -283,6 +300,14 @@ __global__ void __launch_bounds__(kRateThreads, 1) mma_rate_kernel(const RateArg
     const uint32_t trow = tmem_base + ((uint32_t)((warp % 4) * 32) << 16) + (uint32_t)(((warp - 3) / 4) % 4) * 32;
     const uint32_t my = scratch_u + (uint32_t)(tid % 512) * 16;
     uint32_t sink = 0;
+    if (p.copy >= 32 && (p.copy & 8)) {
+      // flag 8: the epilogue warps poll an mbarrier that never completes (as the tower's epilogue does while MMAs run)
+      const uint32_t bw = smem_u32(&bars[3]);
+      while (!done_s) {
+        if (mbar_try_wait(bw, 0)) break;
+        sink += (uint32_t)clock64();
+      }
+    } else
     while (!done_s) {
       uint32_t r[32];
       tmem_ld32(trow, r);
