@@ -4,6 +4,7 @@ Public surface mirrors the reference packages `alphatriangle.nn` and
 `alphatriangle.features` for this one path; see DESIGN.md and INTEGRATION.md.
 """
 
+from .batcher import LeafBatcher
 from .config import EnvConfig, ModelConfig, TrainConfig
 from .features import extract_features_batch, extract_state_features
 from .net import AlphaTriangleNet
@@ -13,6 +14,7 @@ from .packing import pack_states
 __all__ = [
     "AlphaTriangleNet",
     "EnvConfig",
+    "LeafBatcher",
     "ModelConfig",
     "NetworkEvaluationError",
     "NeuralNetwork",

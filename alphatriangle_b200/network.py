@@ -20,6 +20,7 @@ from . import _lib
 from .config import ModelConfig
 from .engine import Engine
 from .net import AlphaTriangleNet
+from . import packing
 from .packing import RECORD_BYTES, pack_states
 
 logger = logging.getLogger(__name__)
@@ -83,7 +84,7 @@ class NeuralNetwork:
                 raise _lib.LibraryError(f"precision {precision!r} unavailable: {_lib.last_error()}")
         else:
             raise ValueError(f"precision must be 'auto', 'fp32' or 'bf16', got {precision!r}")
-        self._action_keys = list(range(self.action_dim))
+        self._action_keys = tuple(range(self.action_dim))
         self._stamp: tuple | None = None
         self._weights_version = 0
         self._sync_engine()
@@ -224,17 +225,14 @@ class NeuralNetwork:
         try:
             probs, values, flags = self._evaluate_rows(states)
             self._raise_for_flags(flags, True, " in batch evaluation")
-            clipped = np.maximum(probs, 0)
-            sums = clipped.sum(axis=1)
-            suspicious = np.abs(sums - 1.0) > 5e-6  # rows the exact per-row rule might touch
-            values_list = values.tolist()
-            keys = self._action_keys
-            results: list[PolicyValueOutput] = []
-            for i in range(len(states)):
-                row = clipped[i]
-                if suspicious[i]:
-                    row = self._finish_policy(probs[i], states[i], f"sample {i}")
-                results.append((dict(zip(keys, row.tolist())), values_list[i]))
+            # dicts and tuples are built in C (csrc/at_pyhost.c: max(p, 0) per entry, cached int keys); rows whose
+            # clipped sum is not within 5e-6 of 1 come back in `recheck` and take the reference's exact per-row rule
+            results, recheck = packing._host().build_results(
+                np.ascontiguousarray(probs, dtype=np.float32), np.ascontiguousarray(values, dtype=np.float32),
+                len(states), self.action_dim, self._action_keys)
+            for i in recheck:
+                row = self._finish_policy(probs[i], states[i], f"sample {i}")
+                results[i] = (dict(zip(self._action_keys, row.tolist())), results[i][1])
         except Exception as e:
             logger.error(f"Error during batch evaluation: {e}", exc_info=True)
             raise NetworkEvaluationError(f"Batch evaluation failed: {e}") from e

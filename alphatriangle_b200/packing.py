@@ -94,19 +94,53 @@ def pack_state_into(rec: np.ndarray, state, rows: int, cols: int, slots: int) ->
     rec["pad"] = 0
 
 
-def pack_states(states, env_config, out: np.ndarray | None = None) -> np.ndarray:
-    """list[GameState] -> uint8 [B, 80] (a view of a PACKED_DTYPE array)."""
+def _host():
+    """The C host loops (csrc/at_pyhost.c), built next to libat_b200.so."""
+    global _pyhost
+    if _pyhost is None:
+        try:
+            from . import _pyhost as mod
+        except ImportError as e:  # same rule as the CUDA library: no silent slow path
+            raise ImportError(
+                "alphatriangle_b200/_pyhost.so not found: build it with `python __graft_entry__.py build` (gcc, Python.h)"
+            ) from e
+        _pyhost = mod
+    return _pyhost
+
+
+_pyhost = None
+
+
+def pack_states_py(states, env_config, out: np.ndarray | None = None) -> np.ndarray:
+    """Pure-Python twin of the C packer: the readable statement of the record format, the packer for array types the C
+    loop does not read directly (anything that is not a one-byte-per-cell array), and the one that words shape errors."""
     check_env(env_config)
     rows, cols, slots = int(env_config.ROWS), int(env_config.COLS), int(env_config.NUM_SHAPE_SLOTS)
     n = len(states)
-    if out is None:
-        recs = np.zeros(n, dtype=PACKED_DTYPE)
-    else:
-        if out.dtype != np.uint8 or out.shape != (n, RECORD_BYTES) or not out.flags.c_contiguous:
-            raise ValueError("out must be a C-contiguous uint8 array of shape [len(states), 80]")
-        recs = out.reshape(-1).view(PACKED_DTYPE)
+    recs = _records(n, out)
     for i, state in enumerate(states):
         pack_state_into(recs[i], state, rows, cols, slots)
+    return recs.view(np.uint8).reshape(n, RECORD_BYTES)
+
+
+def _records(n: int, out: np.ndarray | None) -> np.ndarray:
+    if out is None:
+        return np.zeros(n, dtype=PACKED_DTYPE)
+    if out.dtype != np.uint8 or out.shape != (n, RECORD_BYTES) or not out.flags.c_contiguous:
+        raise ValueError("out must be a C-contiguous uint8 array of shape [len(states), 80]")
+    return out.reshape(-1).view(PACKED_DTYPE)
+
+
+def pack_states(states, env_config, out: np.ndarray | None = None) -> np.ndarray:
+    """list[GameState] -> uint8 [B, 80] (a view of a PACKED_DTYPE array). The loop runs in C (csrc/at_pyhost.c); a batch
+    holding a state whose grid arrays are not plain byte arrays of shape [ROWS, COLS] goes through pack_states_py."""
+    check_env(env_config)
+    rows, cols, slots = int(env_config.ROWS), int(env_config.COLS), int(env_config.NUM_SHAPE_SLOTS)
+    n = len(states)
+    recs = _records(n, out)
+    done = _host().pack_states(states, rows, cols, slots, recs.view(np.uint8).reshape(-1))
+    if done < 0:
+        return pack_states_py(states, env_config, recs.view(np.uint8).reshape(n, RECORD_BYTES))
     return recs.view(np.uint8).reshape(n, RECORD_BYTES)
 
 
