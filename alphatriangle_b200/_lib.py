@@ -47,6 +47,8 @@ EXPORTS = (
     "at_engine_evaluate_packed",
     "at_engine_evaluate_packed_static",
     "at_engine_evaluate_host",
+    "at_engine_submit_host",
+    "at_engine_wait_host",
     "at_engine_last_launches",
     "at_engine_kernel_ms",
     "at_engine_bf16_trunk",
@@ -122,6 +124,8 @@ def _bind(lib: C.CDLL) -> None:
         "at_engine_evaluate_packed": (i32, [vp, i32, vp, i64, vp, vp, vp, vp]),
         "at_engine_evaluate_packed_static": (i32, [vp, vp, i64, vp, vp, vp, vp]),
         "at_engine_evaluate_host": (i32, [vp, i32, vp, i64, vp, vp, vp, vp]),
+        "at_engine_submit_host": (i32, [vp, i32, vp, i64, vp, vp, vp, i32, vp]),
+        "at_engine_wait_host": (i32, [vp, i32]),
         "at_engine_last_launches": (i64, [vp]),
         "at_engine_bf16_trunk": (i32, [vp, vp, i64, vp, vp]),
         "at_engine_kernel_ms": (i32, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),

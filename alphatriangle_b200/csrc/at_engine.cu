@@ -54,6 +54,18 @@ struct at_engine {
   cudaEvent_t slice_done[4] = {nullptr, nullptr, nullptr, nullptr};
   cudaEvent_t copies_done = nullptr;
 
+  // pipelined host entry points (at_engine_submit_host / at_engine_wait_host): two batches in flight, each with its own
+  // device staging, so the PCIe copies of one batch run under the kernels of the other
+  struct HostSlot {
+    void* d_states = nullptr;
+    float *d_policy = nullptr, *d_value = nullptr;
+    uint32_t* d_flags = nullptr;
+    cudaEvent_t staged = nullptr, computed = nullptr, done = nullptr;
+    bool busy = false;
+    int64_t launches = 0;
+  } slot[2];
+  cudaStream_t h2d_stream = nullptr;
+
   Bf16Path* bf16 = nullptr;  // tcgen05 path state (null if the configuration is not covered)
   std::string bf16_reason;
   uint2* heads_frag[2] = {nullptr, nullptr};  // per weight set: head matrices as bf16 MMA fragments (null: shape not covered)
@@ -382,6 +394,16 @@ int at_engine_create(const at_model_desc* desc, int device, int64_t max_batch, a
     AT_TRY(dev_alloc(&e->d_flags, 4));
     AT_CUDA_TRY(cudaMemset(e->d_flags, 0, 4 * sizeof(uint32_t)));
     AT_CUDA_TRY(cudaStreamCreateWithFlags(&e->copy_stream, cudaStreamNonBlocking));
+    AT_CUDA_TRY(cudaStreamCreateWithFlags(&e->h2d_stream, cudaStreamNonBlocking));
+    for (auto& sl : e->slot) {
+      AT_CUDA_TRY(cudaMalloc(&sl.d_states, (size_t)max_batch * AT_STATE_BYTES));
+      AT_TRY(dev_alloc(&sl.d_policy, max_batch * (int64_t)p.action_dim));
+      AT_TRY(dev_alloc(&sl.d_value, max_batch));
+      AT_TRY(dev_alloc(&sl.d_flags, 4));
+      AT_CUDA_TRY(cudaEventCreateWithFlags(&sl.staged, cudaEventDisableTiming));
+      AT_CUDA_TRY(cudaEventCreateWithFlags(&sl.computed, cudaEventDisableTiming));
+      AT_CUDA_TRY(cudaEventCreateWithFlags(&sl.done, cudaEventDisableTiming));
+    }
     for (auto& ev : e->slice_done) AT_CUDA_TRY(cudaEventCreateWithFlags(&ev, cudaEventDisableTiming));
     AT_CUDA_TRY(cudaEventCreateWithFlags(&e->copies_done, cudaEventDisableTiming));
     return AT_OK;
@@ -419,6 +441,16 @@ int at_engine_destroy(at_engine* e) {
   cudaFree(e->d_states);
   cudaFree(e->d_flags);
   if (e->copy_stream) cudaStreamDestroy(e->copy_stream);
+  if (e->h2d_stream) cudaStreamDestroy(e->h2d_stream);
+  for (auto& sl : e->slot) {
+    cudaFree(sl.d_states);
+    cudaFree(sl.d_policy);
+    cudaFree(sl.d_value);
+    cudaFree(sl.d_flags);
+    if (sl.staged) cudaEventDestroy(sl.staged);
+    if (sl.computed) cudaEventDestroy(sl.computed);
+    if (sl.done) cudaEventDestroy(sl.done);
+  }
   for (auto& ev : e->slice_done)
     if (ev) cudaEventDestroy(ev);
   if (e->copies_done) cudaEventDestroy(e->copies_done);
@@ -635,6 +667,47 @@ int at_engine_evaluate_host(at_engine* e, int precision, const void* h_states, i
   AT_CUDA_TRY(cudaEventRecord(e->copies_done, e->copy_stream));
   AT_CUDA_TRY(cudaStreamSynchronize(st));
   AT_CUDA_TRY(cudaEventSynchronize(e->copies_done));
+  return AT_OK;
+}
+
+int at_engine_submit_host(at_engine* e, int precision, const void* h_states, int64_t batch, float* h_policy, float* h_value,
+                          uint32_t* h_flags, int slot, void* stream) {
+  if (!e) return fail(AT_E_INVALID, "at_engine_submit_host: null engine");
+  if (slot < 0 || slot > 1) return fail(AT_E_INVALID, "at_engine_submit_host: slot must be 0 or 1");
+  if (batch <= 0 || batch > e->max_batch) return fail(AT_E_INVALID, "at_engine_submit_host: batch must be in 1..max_batch");
+  if (!h_states || !h_policy || !h_value || !h_flags) return fail(AT_E_INVALID, "at_engine_submit_host: null pointer");
+  at_engine::HostSlot& sl = e->slot[slot];
+  if (sl.busy) return fail(AT_E_INVALID, "at_engine_submit_host: slot still in flight (call at_engine_wait_host first)");
+  DeviceGuard guard(e->device);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  // records go up on their own stream, so they do not queue behind the previous batch's kernels
+  AT_CUDA_TRY(cudaMemcpyAsync(sl.d_states, h_states, (size_t)batch * AT_STATE_BYTES, cudaMemcpyHostToDevice, e->h2d_stream));
+  AT_CUDA_TRY(cudaEventRecord(sl.staged, e->h2d_stream));
+  AT_CUDA_TRY(cudaStreamWaitEvent(st, sl.staged, 0));
+  AT_CUDA_TRY(cudaMemsetAsync(sl.d_flags, 0, sizeof(uint32_t), st));
+  AT_TRY(at_engine_evaluate_packed(e, precision, sl.d_states, batch, sl.d_policy, sl.d_value, sl.d_flags, stream));
+  sl.launches = e->last_launches;
+  AT_CUDA_TRY(cudaEventRecord(sl.computed, st));
+  // results drain on the copy stream while the compute stream is free for the other slot's kernels
+  AT_CUDA_TRY(cudaStreamWaitEvent(e->copy_stream, sl.computed, 0));
+  const int A = e->plan.action_dim;
+  AT_CUDA_TRY(cudaMemcpyAsync(h_policy, sl.d_policy, (size_t)batch * A * sizeof(float), cudaMemcpyDeviceToHost, e->copy_stream));
+  AT_CUDA_TRY(cudaMemcpyAsync(h_value, sl.d_value, (size_t)batch * sizeof(float), cudaMemcpyDeviceToHost, e->copy_stream));
+  AT_CUDA_TRY(cudaMemcpyAsync(h_flags, sl.d_flags, sizeof(uint32_t), cudaMemcpyDeviceToHost, e->copy_stream));
+  AT_CUDA_TRY(cudaEventRecord(sl.done, e->copy_stream));
+  sl.busy = true;
+  return AT_OK;
+}
+
+int at_engine_wait_host(at_engine* e, int slot) {
+  if (!e) return fail(AT_E_INVALID, "at_engine_wait_host: null engine");
+  if (slot < 0 || slot > 1) return fail(AT_E_INVALID, "at_engine_wait_host: slot must be 0 or 1");
+  at_engine::HostSlot& sl = e->slot[slot];
+  if (!sl.busy) return fail(AT_E_INVALID, "at_engine_wait_host: nothing was submitted on this slot");
+  DeviceGuard guard(e->device);
+  sl.busy = false;
+  AT_CUDA_TRY(cudaEventSynchronize(sl.done));
+  e->last_launches = sl.launches;
   return AT_OK;
 }
 

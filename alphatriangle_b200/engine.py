@@ -47,6 +47,8 @@ class Engine:
         self._h_policy = torch.empty((self.max_batch, self.action_dim), dtype=torch.float32, pin_memory=True)
         self._h_value = torch.empty((self.max_batch,), dtype=torch.float32, pin_memory=True)
         self._h_flags = torch.zeros((4,), dtype=torch.int32, pin_memory=True)
+        self._slots: list = [None, None]  # pinned staging of the pipelined host calls, allocated on first use
+        self._slot_batch = [0, 0]
         self._d_flags = torch.zeros((4,), dtype=torch.int32, device=self.device)
 
     def _read_table(self) -> list[tuple[str, int, int]]:
@@ -158,6 +160,43 @@ class Engine:
             "at_engine_evaluate_host",
         )
         return self._h_policy[:b].numpy(), self._h_value[:b].numpy(), int(self._h_flags[0].item())
+
+    # ---- two batches in flight (at_engine_submit_host / at_engine_wait_host) ----
+    def _slot_buffers(self, slot: int):
+        if slot not in (0, 1):
+            raise ValueError("slot must be 0 or 1")
+        if self._slots[slot] is None:
+            self._slots[slot] = (
+                torch.empty((self.max_batch, RECORD_BYTES), dtype=torch.uint8, pin_memory=True),
+                torch.empty((self.max_batch, self.action_dim), dtype=torch.float32, pin_memory=True),
+                torch.empty((self.max_batch,), dtype=torch.float32, pin_memory=True),
+                torch.zeros((4,), dtype=torch.int32, pin_memory=True),
+            )
+        return self._slots[slot]
+
+    def submit_host(self, packed: np.ndarray | torch.Tensor, precision: int, slot: int) -> None:
+        """Queue one batch of host records on `slot` (0 / 1) and return; `wait_host(slot)` delivers the results. While one
+        slot's results drain over PCIe the other slot's kernels run."""
+        b = int(packed.shape[0])
+        if b > self.max_batch or b <= 0:
+            raise ValueError(f"batch {b} outside 1..{self.max_batch}")
+        h_states, h_policy, h_value, h_flags = self._slot_buffers(slot)
+        src = packed if isinstance(packed, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(packed))
+        h_states[:b].copy_(src)
+        _lib.check(
+            self.lib.at_engine_submit_host(self.handle, precision, _ptr(h_states), b, _ptr(h_policy), _ptr(h_value), _ptr(h_flags), slot,
+                                           _stream_ptr(self.device)),
+            "at_engine_submit_host",
+        )
+        self._slot_batch[slot] = b
+
+    def wait_host(self, slot: int):
+        """(probs ndarray [B,A], value ndarray [B], flags int) of the batch submitted on `slot`; views of that slot's pinned
+        staging, valid until the slot is submitted to again."""
+        _lib.check(self.lib.at_engine_wait_host(self.handle, slot), "at_engine_wait_host")
+        _h_states, h_policy, h_value, h_flags = self._slot_buffers(slot)
+        b = self._slot_batch[slot]
+        return h_policy[:b].numpy(), h_value[:b].numpy(), int(h_flags[0].item())
 
     def kernel_times(self) -> dict | None:
         """Device milliseconds of the tower and FC kernels of the last bf16 evaluation (waits for it)."""

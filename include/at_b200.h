@@ -171,6 +171,16 @@ int at_engine_evaluate_packed_static(at_engine* e, const void* d_states, int64_t
 int at_engine_evaluate_host(at_engine* e, int precision, const void* h_states, int64_t batch, float* h_policy, float* h_value,
                             uint32_t* h_flags, void* stream);
 
+/* The same call split in two so that two batches can be in flight: submit queues the copies and kernels of one batch on
+ * `slot` (0 or 1, each with its own device staging) and returns; wait blocks until that slot's probs / values / flags are
+ * in the host buffers given at submit time. While slot 0's results drain over PCIe (5.9 MB per 4096 states) slot 1's
+ * kernels run. A slot must be waited on before it is submitted to again; the host buffers must stay valid (and, for the
+ * copies to be asynchronous, pinned) until the wait returns. The reference's evaluate_batch is synchronous
+ * (alphatriangle/nn/network.py:242-318); this pair is what a batcher serving many searches calls instead. */
+int at_engine_submit_host(at_engine* e, int precision, const void* h_states, int64_t batch, float* h_policy, float* h_value,
+                          uint32_t* h_flags, int slot, void* stream);
+int at_engine_wait_host(at_engine* e, int slot);
+
 /* Introspection used by bench.py: kernels launched by the last evaluate call, and the
  * device time (CUDA events on the launching stream) of the two tcgen05 kernels of the
  * last bf16 evaluation; waits for that evaluation to finish. */
