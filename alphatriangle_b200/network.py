@@ -195,14 +195,26 @@ class NeuralNetwork:
         cap = self.engine.max_batch
         if len(states) <= cap:
             return self.engine.evaluate_host(packed, self.precision)
+        # more states than the engine's staging holds: chunks go through the two host slots, so one chunk's results
+        # come down over PCIe while the next chunk's kernels run
         probs = np.empty((len(states), self.action_dim), dtype=np.float32)
         values = np.empty((len(states),), dtype=np.float32)
         flags = 0
-        for lo in range(0, len(states), cap):
-            p, v, f = self.engine.evaluate_host(packed[lo : lo + cap], self.precision)
+        starts = list(range(0, len(states), cap))
+
+        def collect(k: int) -> int:
+            p, v, f = self.engine.wait_host(k & 1)
+            lo = starts[k]
             probs[lo : lo + cap] = p
             values[lo : lo + cap] = v
-            flags |= f
+            return f
+
+        for k, lo in enumerate(starts):
+            if k >= 2:
+                flags |= collect(k - 2)
+            self.engine.submit_host(packed[lo : lo + cap], self.precision, k & 1)
+        for k in range(max(len(starts) - 2, 0), len(starts)):
+            flags |= collect(k)
         return probs, values, flags
 
     def evaluate_state(self, state) -> PolicyValueOutput:

@@ -53,3 +53,20 @@ def test_slot_protocol_errors():
     assert nn.engine.lib.at_engine_wait_host(nn.engine.handle, 5) != 0 and "slot must be 0 or 1" in _lib.last_error()
     with pytest.raises(ValueError):
         nn.engine.submit_host(pack_states(synth_states(65, env, seed=2), env), nn.precision, 1)
+
+
+def test_evaluate_batch_with_more_states_than_max_batch():
+    """network._evaluate_rows sends the chunks through the two host slots; results keep their order."""
+    env, mc = at.EnvConfig(), at.ModelConfig(USE_TRANSFORMER=False)
+    small = at.NeuralNetwork(mc, env, None, torch.device("cuda:0"), precision="fp32", max_batch=16)
+    big = at.NeuralNetwork(mc, env, None, torch.device("cuda:0"), precision="fp32", max_batch=128)
+    sd = synth_state_dict(small.get_weights(), 21)
+    small.set_weights(sd)
+    big.set_weights(sd)
+    for n in (16, 17, 33, 50, 100):  # 1, 2, 3, 4 and 7 chunks
+        states = synth_states(n, env, seed=300 + n)
+        a, b = small.evaluate_batch(states), big.evaluate_batch(states)
+        assert len(a) == len(b) == n
+        for (da, va), (db, vb) in zip(a, b):
+            assert abs(va - vb) <= 1e-5
+            assert np.abs(np.array(list(da.values())) - np.array(list(db.values()))).max() <= 1e-6
