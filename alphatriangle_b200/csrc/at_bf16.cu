@@ -23,6 +23,7 @@
 
 #include <cstdlib>
 #include <mutex>
+#include <type_traits>
 #include <vector>
 
 #include "at_bf16.cuh"
@@ -118,17 +119,17 @@ __device__ __forceinline__ float act_fn(float x) {
   if constexpr (ACT == AT_ACT_RELU) return fmaxf(x, 0.0f);
   else return apply_act(x, ACT);
 }
-// eight fp32 values -> activation -> bf16, zeroed when `keep` is 0 (padding rows). ReLU commutes with the rounding, so it
-// is applied to the packed pairs (one HMNMX2 per two values) and the row mask is a single AND per pair.
+// eight fp32 values -> activation -> bf16, zeroed when `keep` is 0 (padding rows). ReLU rides on the conversion
+// (cvt.rn.relu.bf16x2.f32) and the row mask is a single AND per pair.
 template <int ACT>
 __device__ __forceinline__ uint4 pack8_act(const float (&v)[8], uint32_t keep) {
   uint32_t w[4];
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
     if constexpr (ACT == AT_ACT_RELU) {
-      __nv_bfloat162 h = __floats2bfloat162_rn(v[2 * i], v[2 * i + 1]);
-      h = __hmax2(h, __floats2bfloat162_rn(0.0f, 0.0f));
-      w[i] = *reinterpret_cast<uint32_t*>(&h) & keep;
+      uint32_t h;  // round-to-nearest conversion with the ReLU clamp built in (negative and NaN inputs give +0)
+      asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(v[2 * i + 1]), "f"(v[2 * i]));
+      w[i] = h & keep;
     } else {
       w[i] = pack_bf16x2(act_fn<ACT>(v[2 * i]), act_fn<ACT>(v[2 * i + 1])) & keep;
     }
@@ -390,27 +391,42 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         uint8_t* gdst = p.fc_a + (((board >> 7) * p.n_kc + (int64_t)pos * (L.cout / 8)) * 128 + (board & 127)) * 16;
         const bool gstore = valid && inside;
         const int cout = (p.debug & 4u) ? 0 : L.cout;
+        // the chunk loop, specialised on (residual, destination) so its body has no per-group branches
+        auto drain = [&](auto HAS_RES, auto TO_SMEM) {
 #pragma unroll 1
-        for (int c0 = eh * 32; c0 < cout; c0 += 32 * kEpiSplit) {
-          uint32_t r[32];
-          tmem_ld32(tmem_row + (uint32_t)c0, r);
-          tmem_ld_wait();
+          for (int c0 = eh * 32; c0 < cout; c0 += 32 * kEpiSplit) {
+            uint32_t r[32];
+            tmem_ld32(tmem_row + (uint32_t)c0, r);
+            tmem_ld_wait();
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const float4 ba = *reinterpret_cast<const float4*>(bias + c0 + i * 8), bb = *reinterpret_cast<const float4*>(bias + c0 + i * 8 + 4);
-            float v[8] = {__uint_as_float(r[i * 8 + 0]) + ba.x, __uint_as_float(r[i * 8 + 1]) + ba.y, __uint_as_float(r[i * 8 + 2]) + ba.z,
-                          __uint_as_float(r[i * 8 + 3]) + ba.w, __uint_as_float(r[i * 8 + 4]) + bb.x, __uint_as_float(r[i * 8 + 5]) + bb.y,
-                          __uint_as_float(r[i * 8 + 6]) + bb.z, __uint_as_float(r[i * 8 + 7]) + bb.w};
-            const int chunk = c0 / 8 + i;
-            if (has_res) {
-              const uint4 rv = lds128(res_u + (uint32_t)chunk * kPlaneBytes);
-              v[0] += bf16_lo(rv.x); v[1] += bf16_hi(rv.x); v[2] += bf16_lo(rv.y); v[3] += bf16_hi(rv.y);
-              v[4] += bf16_lo(rv.z); v[5] += bf16_hi(rv.z); v[6] += bf16_lo(rv.w); v[7] += bf16_hi(rv.w);
+            for (int i = 0; i < 4; ++i) {
+              const float4 ba = *reinterpret_cast<const float4*>(bias + c0 + i * 8), bb = *reinterpret_cast<const float4*>(bias + c0 + i * 8 + 4);
+              float v[8] = {__uint_as_float(r[i * 8 + 0]) + ba.x, __uint_as_float(r[i * 8 + 1]) + ba.y, __uint_as_float(r[i * 8 + 2]) + ba.z,
+                            __uint_as_float(r[i * 8 + 3]) + ba.w, __uint_as_float(r[i * 8 + 4]) + bb.x, __uint_as_float(r[i * 8 + 5]) + bb.y,
+                            __uint_as_float(r[i * 8 + 6]) + bb.z, __uint_as_float(r[i * 8 + 7]) + bb.w};
+              const int chunk = c0 / 8 + i;
+              if constexpr (decltype(HAS_RES)::value) {
+                const uint4 rv = lds128(res_u + (uint32_t)chunk * kPlaneBytes);
+                v[0] += bf16_lo(rv.x); v[1] += bf16_hi(rv.x); v[2] += bf16_lo(rv.y); v[3] += bf16_hi(rv.y);
+                v[4] += bf16_lo(rv.z); v[5] += bf16_hi(rv.z); v[6] += bf16_lo(rv.w); v[7] += bf16_hi(rv.w);
+              }
+              const uint4 out = pack8_act<ACT>(v, keep);
+              if constexpr (decltype(TO_SMEM)::value) {
+                sts128(dst_u + (uint32_t)chunk * kPlaneBytes, out);
+              } else {
+                if (gstore) *reinterpret_cast<uint4*>(gdst + (size_t)chunk * 2048) = out;
+              }
             }
-            const uint4 out = pack8_act<ACT>(v, keep);
-            if (to_smem) sts128(dst_u + (uint32_t)chunk * kPlaneBytes, out);
-            else if (gstore) *reinterpret_cast<uint4*>(gdst + (size_t)chunk * 2048) = out;
           }
+        };
+        using std::false_type;
+        using std::true_type;
+        if (has_res) {
+          if (to_smem) drain(true_type{}, true_type{});
+          else drain(true_type{}, false_type{});
+        } else {
+          if (to_smem) drain(false_type{}, true_type{});
+          else drain(false_type{}, false_type{});
         }
         tc_fence_before();  // TMEM reads are done before the next layer's MMAs overwrite the accumulator
         if (l + 1 < p.n_layers) arrive_act();
