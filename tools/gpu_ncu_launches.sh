@@ -1,5 +1,5 @@
 #!/bin/bash
-# round-1 evidence refresh: plain bench, then the launch list of the same command under ncu (one ncu invocation per gpurun call)
+# gpurun --timeout 900 -- 'bash tools/gpu_ncu_launches.sh'   : plain bench, then the launch list of the same command under ncu
 mkdir -p gpurun_out
 python bench.py --steps 20 --warmup 5 > gpurun_out/bench_final.log 2>&1 || { tail -5 gpurun_out/bench_final.log; exit 1; }
 tail -1 gpurun_out/bench_final.log | cut -c1-400
