@@ -31,3 +31,19 @@ def test_row_shifted_interleaved_operand(n, shift):
     )
     assert status == 0
     assert np.array_equal(out, A[shift : shift + 128] @ B.T)
+
+
+def test_mma_rate_probe_reports_the_pipe_rate():
+    """Two issuing threads on different accumulators retire a 128x128x16 MMA about every 64 cycles."""
+    import torch
+
+    from alphatriangle_b200 import _lib
+
+    lib = _lib.load()
+    src = torch.zeros(1 << 16, dtype=torch.uint8, device="cuda")
+    out = torch.zeros(8, dtype=torch.float32, device="cuda")
+    assert lib.at_probe_mma_rate(128, 1024, 2, 0, 0, src.data_ptr(), 8, out.data_ptr(), None) == 0
+    torch.cuda.synchronize()
+    per_issuer = out.cpu().numpy()
+    assert (per_issuer > 100).all() and (per_issuer < 200).all(), per_issuer  # 128 when the pipe is saturated
+    assert lib.at_probe_mma_rate(100, 1024, 2, 0, 0, src.data_ptr(), 8, out.data_ptr(), None) != 0  # n must be a multiple of 16
