@@ -21,6 +21,7 @@
 
 #include <cuda_bf16.h>
 
+#include <cstdint>
 #include <cstdlib>
 #include <mutex>
 #include <type_traits>
@@ -929,15 +930,27 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
   AT_CUDA_TRY(cudaEventRecord(b->ev[1], st));
   ++*launches;
 
-  // trunk FC: split-K so that M-tiles x splits covers the SMs about twice
+  // trunk FC: split-K. One CTA per SM (128 KB ring), so the launch runs in whole waves of `sms` CTAs: take the split count
+  // that minimises waves x slabs per CTA (at batch 4096: 32 M-tiles x 9 splits = 288 CTAs = two waves of 27 slabs, where
+  // 10 splits would spill 24 CTAs into a third wave).
   const int m_tiles = (int)((batch + 127) / 128);
   const int n_slabs = b->n_kc / 8;
-  int splits = (2 * b->sms + m_tiles - 1) / m_tiles;
-  if (splits > b->max_splits) splits = b->max_splits;
-  if (splits > n_slabs) splits = n_slabs;
-  if (splits < 1) splits = 1;
-  const int per = (n_slabs + splits - 1) / splits;
-  splits = (n_slabs + per - 1) / per;
+  int splits = 1, per = n_slabs;
+  {
+    int64_t best = INT64_MAX;
+    const int cap = b->max_splits < n_slabs ? b->max_splits : n_slabs;
+    for (int sp = 1; sp <= cap; ++sp) {
+      const int pr = (n_slabs + sp - 1) / sp;
+      if ((n_slabs + pr - 1) / pr != sp) continue;  // same work as a smaller split count
+      const int64_t waves = ((int64_t)m_tiles * sp + b->sms - 1) / b->sms;
+      const int64_t cost = waves * (pr + 2);  // + ring fill / accumulator drain per CTA
+      if (cost < best) {
+        best = cost;
+        splits = sp;
+        per = pr;
+      }
+    }
+  }
   FcParams fp{b->fc_a, b->wfc[slot], b->partial, batch, b->n_kc, b->fc_n, per, n_slabs, b->status};
   AT_CUDA_TRY(cudaEventRecord(b->ev[2], st));
   fc_kernel<<<dim3((unsigned)m_tiles, (unsigned)splits), kFcThreads, fc_smem_bytes(), st>>>(fp);
