@@ -441,7 +441,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
 }
 
 // ---- trunk FC: split-K tcgen05 GEMM ---------------------------------------------------------
-constexpr int kFcStages = 4;
+constexpr int kFcStages = 3;  // 96 KB: two CTAs per SM, one CTA's ring fill / accumulator drain under the other's stream
 constexpr int kFcThreads = 192;
 
 struct FcParams {
@@ -455,7 +455,7 @@ struct FcParams {
 
 constexpr size_t fc_smem_bytes() { return (size_t)kFcStages * 2 * kStageBytes + (2 * kFcStages + 1) * 8 + 16; }
 
-__global__ void __launch_bounds__(kFcThreads, 1) fc_kernel(const __grid_constant__ FcParams p) {
+__global__ void __launch_bounds__(kFcThreads, 2) fc_kernel(const __grid_constant__ FcParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kFcStages * 2 * kStageBytes);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * kFcStages + 1);
@@ -942,7 +942,7 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
     for (int sp = 1; sp <= cap; ++sp) {
       const int pr = (n_slabs + sp - 1) / sp;
       if ((n_slabs + pr - 1) / pr != sp) continue;  // same work as a smaller split count
-      const int64_t waves = ((int64_t)m_tiles * sp + b->sms - 1) / b->sms;
+      const int64_t waves = ((int64_t)m_tiles * sp + 2 * b->sms - 1) / (2 * b->sms);  // two CTAs per SM
       const int64_t cost = waves * (pr + 2);  // + ring fill / accumulator drain per CTA
       if (cost < best) {
         best = cost;
