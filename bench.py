@@ -35,7 +35,9 @@ UNIT = "states/s"
 FLOP_PER_STATE = {"conv_only": 167_855_872, "default_tf": 245_516_032}  # 2 FLOP/MAC, no padding credited
 # dram__bytes_read.sum + dram__bytes_write.sum of tower_kernel from the `ncu --set full` capture in profiles/ (per launch, batch 4096):
 # 1.73 MB read + 72.0 MB written (the 126 MB of FC operand tiles it produces mostly stay in the 126 MB L2)
-TOWER_DRAM_BYTES_PER_LAUNCH = {4096: 73_733_376}
+# dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, one launch at batch 4096, from the committed ncu --set full
+# captures (profiles/r01_ncu_full_step_final_raw.csv, profiles/r01_ncu_full_tower_tf_raw.csv); other batch sizes: not captured
+TOWER_DRAM_BYTES_PER_LAUNCH = {("conv_only", 4096): 1_825_792 + 72_273_664, ("default_tf", 4096): 2_452_224 + 75_853_568}
 # dominant kernel's own algorithmic FLOPs: conv_body + res_body (69,120 + 4,423,680 + 17,694,720 + 4 x 35,389,440), plus the two
 # encoder layers (2 x 38,830,080) when they are fused into it
 TOWER_FLOP_PER_STATE = {"conv_only": 163_745_280, "default_tf": 163_745_280 + 77_660_160}
@@ -320,7 +322,7 @@ def run_ours(args):
                     "sync_ms_per_step": e2e_sync_s * 1e3 / e2e_steps},
             "gpu_launches": int(launches_per_step * args.steps),
             "roofline": {"bound": "tensor", "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-                         "traffic": TOWER_DRAM_BYTES_PER_LAUNCH.get(B) if (kern and args.workload == "conv_only") else None, "kernel": (kern or {}).get("name", "whole step (all kernels of the path)"),
+                         "traffic": TOWER_DRAM_BYTES_PER_LAUNCH.get((args.workload, B)) if kern else None, "kernel": (kern or {}).get("name", "whole step (all kernels of the path)"),
                          "kernel_ms": (kern or {}).get("ms"), "fc_kernel_ms": (kern or {}).get("fc_ms"),
                          "kernel_share_of_step": (kern or {}).get("share_of_step"),
                          "peak_source": f"{peaks['source']} bf16 dense, {'sustained' if peak == peaks['sustained'] else 'burst'}",
