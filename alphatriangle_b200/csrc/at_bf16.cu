@@ -175,7 +175,7 @@ __device__ __forceinline__ void issue_slab1(uint32_t tmem_d, uint32_t a16, uint3
 //                     bitmasks, then per layer tcgen05.ld -> +bias (+residual) -> activation -> bf16 -> next image
 //
 // The two boards are independent pipelines that share only the weight ring: while one board's epilogue drains its
-// accumulator (tensor-memory reads run at ~64 B/clock) the other board's MMAs can keep the tensor pipe busy.
+// accumulator the other board's MMAs can keep the tensor pipe busy.
 //
 // What was measured on the way here (profiles/r01_tower_*.txt, r01_mma_rate_probe.txt):
 //  * two issuing threads on different accumulators saturate the pipe at 64 cycles per 128x128x16 MMA, also while bulk copies

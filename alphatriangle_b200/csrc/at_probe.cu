@@ -210,7 +210,54 @@ __global__ void __launch_bounds__(kRateThreads, 1) mma_rate_kernel(const RateArg
   tc_fence_after();
   const uint32_t tmem_base = tmem_base_s;
 
-  if (p.copy >= 10 && p.copy < 20) {
+  if (p.copy >= 64 && p.copy < 80) {
+    // tensor-memory read bandwidth (out[cta] = bytes per cycle over the whole SM): `epi_warps` warps (<= 16) issue back-to-back
+    // tcgen05.ld of one shape, `mmas` rounds each, no other work. copy = 64: 32x32b.x32 (128 B per thread), 65: 32x32b.x16,
+    // 66: 16x256b.x8 (128 B per thread, 16 lanes x 64 columns), 67: 16x128b.x8 (64 B per thread), 68: 32x32b.x64 (256 B per thread)
+    const int ew = warp - 3;
+    if (ew >= 0 && ew < p.epi_warps) {
+      const uint32_t ta = tmem_base + ((uint32_t)((warp % 4) * 32) << 16) + (uint32_t)((ew / 4) % 4) * 64;
+      uint32_t sink = 0;
+      __syncwarp();
+      const long long t0 = clock64();
+      for (int i = 0; i < p.mmas; ++i) {
+        uint32_t r[64];
+        if (p.copy == 64) {
+          asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                       : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                       : "r"(ta) : "memory");
+          sink += r[0] + r[31];
+        } else if (p.copy == 65) {
+          asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                       : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                       : "r"(ta) : "memory");
+          sink += r[0] + r[15];
+        } else if (p.copy == 66) {
+          asm volatile("tcgen05.ld.sync.aligned.16x256b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31}, [%32];"
+                       : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+                       : "r"(ta) : "memory");
+          sink += r[0] + r[31];
+        } else if (p.copy == 67) {
+          asm volatile("tcgen05.ld.sync.aligned.16x128b.x8.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+                       : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                       : "r"(ta) : "memory");
+          sink += r[0] + r[15];
+        } else {
+          asm volatile("tcgen05.ld.sync.aligned.32x32b.x64.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32,%33,%34,%35,%36,%37,%38,%39,%40,%41,%42,%43,%44,%45,%46,%47,%48,%49,%50,%51,%52,%53,%54,%55,%56,%57,%58,%59,%60,%61,%62,%63}, [%64];"
+                       : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31]), "=r"(r[32]), "=r"(r[33]), "=r"(r[34]), "=r"(r[35]), "=r"(r[36]), "=r"(r[37]), "=r"(r[38]), "=r"(r[39]), "=r"(r[40]), "=r"(r[41]), "=r"(r[42]), "=r"(r[43]), "=r"(r[44]), "=r"(r[45]), "=r"(r[46]), "=r"(r[47]), "=r"(r[48]), "=r"(r[49]), "=r"(r[50]), "=r"(r[51]), "=r"(r[52]), "=r"(r[53]), "=r"(r[54]), "=r"(r[55]), "=r"(r[56]), "=r"(r[57]), "=r"(r[58]), "=r"(r[59]), "=r"(r[60]), "=r"(r[61]), "=r"(r[62]), "=r"(r[63])
+                       : "r"(ta) : "memory");
+          sink += r[0] + r[63];
+        }
+        tmem_ld_wait();
+      }
+      const long long t1 = clock64();
+      if (ew == 0 && lane == 0) {
+        const float bytes_per_thread = p.copy == 64 || p.copy == 66 ? 128.0f : (p.copy == 68 ? 256.0f : 64.0f);
+        p.out[blockIdx.x] = bytes_per_thread * 32.0f * (float)p.epi_warps * (float)p.mmas / (float)(t1 - t0);
+      }
+      if (sink == 0x12345678u) p.out[0] = 0.0f;
+    }
+  } else if (p.copy >= 10 && p.copy < 20) {
     // latency variants (out[cta] = cycles per round): 10 / 11 = mbarrier ping-pong between two warps (try_wait / test_wait),
     // 12 = tcgen05.commit -> mbarrier with an empty pipe, 13 = one MMA + commit -> mbarrier (issue-to-completion latency)
     const uint32_t b0 = smem_u32(&bars[0]), b1 = smem_u32(&bars[1]);

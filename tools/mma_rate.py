@@ -47,3 +47,8 @@ print("C. latencies, cycles per round (a ping-pong round holds two hand-offs)")
 for name, v in (("mbarrier ping-pong between two warps, try_wait", 10), ("mbarrier ping-pong between two warps, test_wait", 11),
                 ("tcgen05.commit -> mbarrier, empty pipe", 12), ("one MMA + tcgen05.commit -> mbarrier", 13)):
     print(f"{name:48s}: {run(128, 2000, 1, v, 0)}")
+
+print("D. tensor-memory read bandwidth, bytes per cycle per SM (w warps issuing back-to-back tcgen05.ld + wait::ld)")
+for name, v in (("32x32b.x32", 64), ("32x32b.x16", 65), ("16x256b.x8", 66), ("16x128b.x8", 67), ("32x32b.x64", 68)):
+    for w in (1, 4, 8, 16):
+        print(f"{name:12s} warps={w:2d}: {run(128, 2000, 1, v, w)}")
