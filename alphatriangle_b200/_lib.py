@@ -41,6 +41,7 @@ EXPORTS = (
     "at_engine_weight_entries",
     "at_engine_weight_entry",
     "at_engine_load_weights",
+    "at_engine_publish_weights",
     "at_engine_weight_version",
     "at_engine_supports",
     "at_engine_forward",
@@ -118,6 +119,7 @@ def _bind(lib: C.CDLL) -> None:
         "at_engine_weight_entries": (i32, [vp]),
         "at_engine_weight_entry": (i32, [vp, i32, C.POINTER(C.c_char_p), C.POINTER(i64), C.POINTER(i64)]),
         "at_engine_load_weights": (i32, [vp, vp, i64, i64, vp]),
+        "at_engine_publish_weights": (i32, [vp, vp, i64, i64, vp]),
         "at_engine_weight_version": (i64, [vp]),
         "at_engine_supports": (i32, [vp, i32]),
         "at_engine_forward": (i32, [vp, i32, vp, vp, i64, vp, vp, vp, vp]),

@@ -57,6 +57,15 @@ constexpr int kTowerThreads = 64 + kEpiWarps * 32 + 32;
 constexpr int kMaxBars = 32;                 // mbarrier slots reserved in shared memory
 constexpr long long kTimeoutCycles = 2000000000LL;  // ~1 s: a wedged pipeline reports instead of hanging
 
+// Timing experiments (tools/tower_time.py, tools/tf_time.py) switch parts of the kernels off through TowerParams::debug.
+// They exist only in the experiments build (make experiments -> libat_b200_exp.so, -DAT_EXPERIMENTS); in the product
+// library the tests below are compile-time false and the environment is never read.
+#ifdef AT_EXPERIMENTS
+#define AT_DBG(bits) ((p.debug & (bits)) != 0)
+#else
+#define AT_DBG(bits) false
+#endif
+
 struct TowerLayer {
   int cin, cout, taps, ks, n_slabs;
   int src, dst, res;  // buffer ids 0/1; dst = 2 -> global FC operand; res = -1 -> none
@@ -82,7 +91,7 @@ struct TowerParams {
   int n_kc;                // L * C_last / 8
   int rows, cols;
   uint32_t* status;
-  uint32_t debug;  // timing experiments only (AT_TOWER_DEBUG): 1 no weight copies, 2 no MMAs, 4 no epilogue math, 8 no layer 0, 16 no weight ring
+  uint32_t debug;  // experiments build only (AT_TOWER_DEBUG): 1 no weight copies, 2 no MMAs, 4 no epilogue math, 8 no layer 0, 16 no weight ring
 };
 
 constexpr size_t tower_smem_bytes() {
@@ -205,7 +214,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + NS);
   const uint32_t bar_acc0 = smem_u32(bars + 2 * NS), bar_acc1 = smem_u32(bars + 2 * NS + 1);  // accumulator of board b complete
   const uint32_t bar_act0 = smem_u32(bars + 2 * NS + 2), bar_act1 = smem_u32(bars + 2 * NS + 3);  // input image of board b written
-  const bool use_ring = !(p.debug & 16u);  // 16: timing experiment without the weight ring (issue loop + MMAs + epilogue only)
+  const bool use_ring = !AT_DBG(16u);  // 16: timing experiment without the weight ring (issue loop + MMAs + epilogue only)
 
   // ---- one-time setup --------------------------------------------------------------------
   for (int i = tid; i < kBoards * 2 * kBufBytes / 16; i += kTowerThreads) reinterpret_cast<uint4*>(act)[i] = make_uint4(0, 0, 0, 0);
@@ -251,7 +260,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
           for (int s = 0; s < n_slabs; ++s) {
             ok = wait_bar(bar_empty + 8 * stage, phase ^ 1, p.status, 1u);
             if (!ok) break;
-            if (p.debug & 1u) {
+            if (AT_DBG(1u)) {
               mbar_arrive(bar_full + 8 * stage);
             } else {
               mbar_arrive_expect_tx(bar_full + 8 * stage, bytes);
@@ -272,7 +281,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     const uint32_t my_acc = me == 0 ? bar_acc0 : bar_acc1, my_act = me == 0 ? bar_act0 : bar_act1;
     const uint32_t tmem_d = tmem_base + (uint32_t)me * 128;
     const uint32_t a_lo_fixed = (uint32_t)(kPlaneBytes >> 4) << 16;  // LBO = one 8-channel plane
-    const bool no_mma = (p.debug & 2u) != 0;
+    const bool no_mma = AT_DBG(2u);
     uint32_t stage = 0, phase = 0, lphase = 0;
     bool ok = true;
     for (int64_t pair = pair0; pair < n_pairs && ok; pair += gridDim.x) {
@@ -344,9 +353,9 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
       const bool valid = board < p.batch;
       // The previous board's last epilogue may still be reading its residual from image 0 in the sibling warp (other
       // channel share, same rows): all eight epilogue warps of this board finish it before anyone writes the new image.
-      if (!(p.debug & 64u)) asm volatile("bar.sync %0, %1;" ::"r"(1 + eb), "r"(kEpiWarps / kBoards * 32) : "memory");
+      if (!AT_DBG(64u)) asm volatile("bar.sync %0, %1;" ::"r"(1 + eb), "r"(kEpiWarps / kBoards * 32) : "memory");
       // ---- layer 0 on CUDA cores, straight from the bitmasks (extractor.py:33-46 + conv_body.0) ----
-      if (!(p.debug & 8u)) {
+      if (!AT_DBG(8u)) {
         float g[9];
 #pragma unroll
         for (int t = 0; t < 9; ++t) g[t] = 0.0f;
@@ -391,7 +400,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         const uint32_t dst_u = my_act_u + (uint32_t)(to_smem ? L.dst : 0) * kBufBytes;
         uint8_t* gdst = p.fc_a + (((board >> 7) * p.n_kc + (int64_t)pos * (L.cout / 8)) * 128 + (board & 127)) * 16;
         const bool gstore = valid && inside;
-        const int cout = (p.debug & 4u) ? 0 : L.cout;
+        const int cout = AT_DBG(4u) ? 0 : L.cout;
         // the chunk loop, specialised on (residual, destination) so its body has no per-group branches
         auto drain = [&](auto HAS_RES, auto TO_SMEM) {
 #pragma unroll 1
@@ -903,10 +912,12 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
   tp.b0 = folded + b->b0_off;
   tp.fc_a = b->fc_a;
   tp.status = b->status;
+#ifdef AT_EXPERIMENTS
   {
     const char* dbg = getenv("AT_TOWER_DEBUG");
     tp.debug = dbg ? (uint32_t)atoi(dbg) : 0u;
   }
+#endif
   const int64_t n_pairs = (batch + kBoards - 1) / kBoards;
   const unsigned grid = (unsigned)(n_pairs < b->sms ? n_pairs : b->sms);
   AT_CUDA_TRY(cudaEventRecord(b->ev[0], st));
@@ -1029,21 +1040,41 @@ static int static_scratch_base(unsigned char** out) {
 
 int64_t bf16_static_max_batch() { return 128; }
 
-int bf16_trunk_partials_static(Bf16Path* b, const Plan& p, const float* folded, int slot, const void* d_states, int64_t batch,
-                               int* n_splits, const float** partial, const float** other, cudaStream_t st, int64_t* launches) {
+namespace {
+struct StaticCarve {
+  size_t fc_a, partial, other, grid, total;  // byte sizes of the four regions, each rounded up to 256
+};
+StaticCarve static_carve(const Bf16Path* b, const Plan& p) {
+  const size_t cap = (size_t)bf16_static_max_batch();
+  auto up = [](size_t v) { return (v + 255) & ~size_t(255); };
+  StaticCarve c;
+  c.fc_a = up((size_t)b->n_kc * 2048);  // one 128-board tile of A-operand chunks
+  c.partial = up((size_t)(b->max_splits + 1) * cap * b->fc_n * sizeof(float));
+  c.other = up(cap * p.d.other_dim * sizeof(float));
+  c.grid = up(cap * p.d.env.rows * p.d.env.cols * sizeof(float));
+  c.total = c.fc_a + c.partial + c.other + c.grid;
+  return c;
+}
+}  // namespace
+
+// The two refusals of the static entry point, callable before anything is queued on the stream.
+int bf16_static_check(const Bf16Path* b, const Plan& p, int64_t batch) {
   const int64_t cap = bf16_static_max_batch();
   if (batch > cap)
     return fail(AT_E_INVALID, "at_engine_evaluate_packed_static: batch " + std::to_string(batch) + " exceeds the static scratch limit of " +
                                   std::to_string(cap) + " states; use at_engine_evaluate_packed for larger batches");
-  auto up = [](size_t v) { return (v + 255) & ~size_t(255); };
-  const size_t need_fc_a = up((size_t)b->n_kc * 2048);  // one 128-board tile of A-operand chunks
-  const size_t need_partial = up((size_t)(b->max_splits + 1) * cap * b->fc_n * sizeof(float));
-  const size_t need_other = up((size_t)cap * p.d.other_dim * sizeof(float));
-  const size_t need_grid = up((size_t)cap * p.d.env.rows * p.d.env.cols * sizeof(float));
-  const size_t need = need_fc_a + need_partial + need_other + need_grid;
+  const size_t need = static_carve(b, p).total;
   if (need > kStaticScratchBytes)
     return fail(AT_E_UNSUPPORTED, "at_engine_evaluate_packed_static: this model needs " + std::to_string(need) +
                                       " bytes of scratch, the static array holds " + std::to_string(kStaticScratchBytes));
+  return AT_OK;
+}
+
+int bf16_trunk_partials_static(Bf16Path* b, const Plan& p, const float* folded, int slot, const void* d_states, int64_t batch,
+                               int* n_splits, const float** partial, const float** other, cudaStream_t st, int64_t* launches) {
+  AT_TRY(bf16_static_check(b, p, batch));
+  const StaticCarve c = static_carve(b, p);
+  const size_t need_fc_a = c.fc_a, need_partial = c.partial, need_other = c.other;
   unsigned char* base = nullptr;
   AT_TRY(static_scratch_base(&base));
   // Nothing in the array has to start at zero: rows < batch of every region are fully rewritten by the kernels before

@@ -28,6 +28,7 @@ int bf16_finish_trunk(Bf16Path* p, const Plan& plan, const float* d_folded, int 
 // Same as bf16_trunk_partials with every intermediate buffer inside the library's static device array
 // (no allocation, batch <= bf16_static_max_batch()); *partial / *other point into that array.
 int64_t bf16_static_max_batch();
+int bf16_static_check(const Bf16Path* p, const Plan& plan, int64_t batch);  // batch / scratch-size refusals, nothing queued
 int bf16_trunk_partials_static(Bf16Path* p, const Plan& plan, const float* d_folded, int slot, const void* d_states, int64_t batch,
                                int* n_splits, const float** partial, const float** other, cudaStream_t stream, int64_t* launches);
 const uint32_t* bf16_status_ptr(const Bf16Path* p);  // device word: non-zero if a pipeline wait timed out

@@ -36,6 +36,7 @@ struct at_engine {
   cudaEvent_t ready[2] = {nullptr, nullptr};     // folding of set i finished
   cudaEvent_t last_use[2] = {nullptr, nullptr};  // last evaluation that read set i
   int active = -1;
+  int pending = -1;  // set filled by at_engine_publish_weights, promoted to `active` by the first evaluation that finds it ready
   int64_t version[2] = {-1, -1};
 
   // scratch (fp32 path)
@@ -257,6 +258,11 @@ int forward_fp32_chunk(at_engine* e, const float* W, const float* grid, const fl
 
 int begin_eval(at_engine* e, cudaStream_t st, const float** W) {
   if (e->active < 0) return fail(AT_E_STATE, "evaluate called before at_engine_load_weights");
+  // a published set takes over once its fold / repack has finished; until then evaluations keep reading the old one
+  if (e->pending >= 0 && cudaEventQuery(e->ready[e->pending]) == cudaSuccess) {
+    e->active = e->pending;
+    e->pending = -1;
+  }
   AT_CUDA_TRY(cudaStreamWaitEvent(st, e->ready[e->active], 0));
   *W = e->folded[e->active];
   e->last_launches = 0;
@@ -323,18 +329,11 @@ static HeadsParams heads_params(const at_engine* e, const float* W, int slot) {
   return hp;
 }
 
-// AT_HEADS_MODE=0: the CUDA-core head kernel; 1: tensor-core heads fed by the feature kernel (A/B timing only)
-static int heads_mode() {
-  static const int mode = [] {
-    const char* m = getenv("AT_HEADS_MODE");
-    return (m && m[0] >= '0' && m[0] <= '2') ? m[0] - '0' : 2;
-  }();
-  return mode;
-}
-
-static bool heads_use_mma(const HeadsParams& hp) { return heads_mode() != 0 && hp.frags && heads_mma_supported(hp); }
+// Head widths decide the kernel: heads_mma_kernel (warp-level MMAs on fragment-packed weights) when the trunk and both
+// hidden layers are 64 or 128 wide, else heads_fused_kernel (same fusion on CUDA cores); deeper heads take the unfused tail.
+static bool heads_use_mma(const HeadsParams& hp) { return hp.frags && heads_mma_supported(hp); }
 static bool heads_take_states(const at_engine* e, const HeadsParams& hp) {
-  return heads_mode() == 2 && heads_use_mma(hp) && heads_fused_supported(hp) && e->plan.d.env.cols <= 32;
+  return heads_use_mma(hp) && heads_fused_supported(hp) && e->plan.d.env.cols <= 32;
 }
 
 // Trunk finish + heads + softmax epilogues in one launch: tensor-core variant when the packed fragments exist.
@@ -469,16 +468,18 @@ int at_engine_weight_entry(const at_engine* e, int index, const char** name, int
   return AT_OK;
 }
 
-int at_engine_load_weights(at_engine* e, const float* d_image, int64_t n_floats, int64_t version, void* stream) {
-  if (!e || !d_image) return fail(AT_E_INVALID, "at_engine_load_weights: null argument");
+static int fill_weight_set(at_engine* e, const float* d_image, int64_t n_floats, int64_t version, void* stream, bool deferred,
+                           const char* who) {
+  if (!e || !d_image) return fail(AT_E_INVALID, std::string(who) + ": null argument");
   if (n_floats != e->plan.image_floats)
-    return fail(AT_E_INVALID, "at_engine_load_weights: image has " + std::to_string(n_floats) + " floats, model needs " +
+    return fail(AT_E_INVALID, std::string(who) + ": image has " + std::to_string(n_floats) + " floats, model needs " +
                                   std::to_string(e->plan.image_floats));
   DeviceGuard guard(e->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int target = e->active < 0 ? 0 : 1 - e->active;
-  // evaluations that still read the set about to be overwritten must drain first
+  // evaluations that still read the set about to be overwritten must drain first; so must an earlier publication into it
   AT_CUDA_TRY(cudaStreamWaitEvent(st, e->last_use[target], 0));
+  if (e->pending == target) AT_CUDA_TRY(cudaStreamWaitEvent(st, e->ready[target], 0));
   AT_TRY(fold_weights(e->plan, d_image, e->folded[target], st));
   if (e->bf16) AT_TRY(bf16_pack_weights(e->bf16, e->plan, e->folded[target], target, st));
   if (e->heads_frag[target]) {
@@ -487,8 +488,21 @@ int at_engine_load_weights(at_engine* e, const float* d_image, int64_t n_floats,
   }
   AT_CUDA_TRY(cudaEventRecord(e->ready[target], st));
   e->version[target] = version;
-  e->active = target;
+  if (deferred && e->active >= 0) {
+    e->pending = target;
+  } else {
+    e->active = target;
+    e->pending = -1;
+  }
   return AT_OK;
+}
+
+int at_engine_load_weights(at_engine* e, const float* d_image, int64_t n_floats, int64_t version, void* stream) {
+  return fill_weight_set(e, d_image, n_floats, version, stream, /*deferred=*/false, "at_engine_load_weights");
+}
+
+int at_engine_publish_weights(at_engine* e, const float* d_image, int64_t n_floats, int64_t version, void* stream) {
+  return fill_weight_set(e, d_image, n_floats, version, stream, /*deferred=*/true, "at_engine_publish_weights");
 }
 
 int64_t at_engine_weight_version(const at_engine* e) { return (e && e->active >= 0) ? e->version[e->active] : -1; }
@@ -540,20 +554,25 @@ int at_engine_evaluate_packed_static(at_engine* e, const void* d_states, int64_t
   const Plan& p = e->plan;
   if (!(p.shared.size() == 1 && p.policy.size() == 2 && p.value.size() == 2))
     return fail(AT_E_UNSUPPORTED, "at_engine_evaluate_packed_static: needs one shared FC layer and one hidden layer per head");
+  // every refusal happens before anything is queued: a failed call leaves no kernels behind and the outputs untouched
+  if (!heads_fused_supported(heads_params(e, nullptr, 0)))
+    return fail(AT_E_UNSUPPORTED, "at_engine_evaluate_packed_static: head widths outside what the fused head kernel covers");
+  AT_TRY(bf16_static_check(e->bf16, p, batch));
   DeviceGuard guard(e->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const float* W = nullptr;
   AT_TRY(begin_eval(e, st, &W));
   int splits = 0;
   const float *partial = nullptr, *other = nullptr;
-  AT_TRY(bf16_trunk_partials_static(e->bf16, p, W, e->active, d_states, batch, &splits, &partial, &other, st, &e->last_launches));
-  HeadsParams hp = heads_params(e, W, e->active);
-  hp.partial = partial; hp.splits = splits; hp.other = other; hp.batch = batch;
-  hp.probs = d_policy; hp.value = d_value; hp.flags = d_flags; hp.status = bf16_status_ptr(e->bf16);
-  if (!heads_fused_supported(hp))
-    return fail(AT_E_UNSUPPORTED, "at_engine_evaluate_packed_static: head widths outside what the fused head kernel covers");
-  AT_TRY(run_heads_fused(e, hp, st));
-  return end_eval(e, st);
+  int rc = bf16_trunk_partials_static(e->bf16, p, W, e->active, d_states, batch, &splits, &partial, &other, st, &e->last_launches);
+  if (rc == AT_OK) {
+    HeadsParams hp = heads_params(e, W, e->active);
+    hp.partial = partial; hp.splits = splits; hp.other = other; hp.batch = batch;
+    hp.probs = d_policy; hp.value = d_value; hp.flags = d_flags; hp.status = bf16_status_ptr(e->bf16);
+    rc = run_heads_fused(e, hp, st);
+  }
+  const int rc_end = end_eval(e, st);  // also after a failed launch: whatever was queued still reads this weight set
+  return rc != AT_OK ? rc : rc_end;
 }
 
 int at_engine_forward(at_engine* e, int precision, const float* d_grid, const float* d_other, int64_t batch, float* d_policy,
@@ -589,13 +608,14 @@ int at_engine_evaluate_packed(at_engine* e, int precision, const void* d_states,
   if (!d_states || !d_policy || !d_value || !d_flags) return fail(AT_E_INVALID, "at_engine_evaluate_packed: null pointer");
   if ((reinterpret_cast<uintptr_t>(d_states) & 15u) != 0) return fail(AT_E_INVALID, "at_engine_evaluate_packed: d_states must be 16-byte aligned");
   AT_TRY(check_precision(e, precision));
+  if (precision == AT_PREC_BF16 && batch > e->max_batch)
+    return fail(AT_E_INVALID, "at_engine_evaluate_packed: batch exceeds the engine's max_batch");
   DeviceGuard guard(e->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const float* W = nullptr;
   AT_TRY(begin_eval(e, st, &W));
   const Plan& p = e->plan;
   if (precision == AT_PREC_BF16) {
-    if (batch > e->max_batch) return fail(AT_E_INVALID, "at_engine_evaluate_packed: batch exceeds the engine's max_batch");
     int splits = 0;
     // the tensor-core head kernel derives the other-feature vectors itself: no separate feature launch on this path
     const bool heads_own_other = heads_shape_fused(p) && heads_take_states(e, heads_params(e, W, e->active));

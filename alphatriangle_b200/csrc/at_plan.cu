@@ -15,7 +15,7 @@ struct Builder {
   int64_t add(const std::string& name, int64_t numel) {
     p.image.push_back({name, img, numel});
     const int64_t off = img;
-    img += numel;
+    img += (numel + 3) & ~int64_t(3);  // every tensor starts 16-byte aligned: the image doubles as the trainer's parameter storage
     return off;
   }
   int64_t reserve(int64_t floats) {

@@ -3,15 +3,17 @@
 The path shards by game: every rank evaluates its own states with a full weight
 replica, and the only exchange is the trainer publishing new weights. The
 reference does that with `ray.put(get_weights())` + `set_weights.remote(...)` on
-every worker (alphatriangle/training/worker_manager.py:169-209, triggered from
-training/loop.py:271-287). Here it is ONE broadcast of the flat fp32 weight
-image (order = at_model_describe) plus a small int64 header (version =
-trainer global_step, and the BatchNorm `num_batches_tracked` counters, which are
-the only non-float entries of the state_dict). The receiver folds / repacks the
-image on its GPU straight out of the receive buffer (at_engine_load_weights)
-into the engine's inactive weight set, so in-flight batches keep reading the old
-set. Backend: NCCL over NVLink for CUDA tensors; the same code runs over gloo
-with CPU tensors, which is how the host logic is tested without GPUs.
+every worker while the workers keep playing (alphatriangle/training/worker_manager.py:169-209,
+triggered from training/loop.py:271-287). Here it is ONE collective over ONE
+pre-registered buffer: every rank's parameters already live inside a flat fp32
+image (flat.py), whose int64 tail carries the version (trainer global_step) and the
+BatchNorm `num_batches_tracked` counters -- nothing is packed before the send or
+unpacked after the receive, and no value comes back to the host in between. The
+receiver folds / repacks the image on its GPU straight out of that buffer into the
+engine's inactive weight set on a side stream, while evaluations on the main
+stream keep reading the old set (at_engine_publish_weights). Backend: NCCL over
+NVLink for CUDA tensors; the same code runs over gloo with CPU tensors, which is
+how the host logic is tested without GPUs.
 """
 
 from __future__ import annotations
@@ -21,70 +23,63 @@ import time
 import torch
 import torch.distributed as dist
 
-
-def float_table(state_dict, table):
-    """[(key, offset, numel)] restricted / checked against a state_dict."""
-    for key, _off, numel in table:
-        if key not in state_dict or state_dict[key].numel() != numel:
-            raise KeyError(f"state_dict does not match the weight table at {key!r}")
-    return table
+from .flat import FlatWeights
 
 
-def int_keys(state_dict) -> list[str]:
-    return [k for k, v in state_dict.items() if not v.dtype.is_floating_point]
+def broadcast_flat(flat: FlatWeights, src: int, version: int, group=None) -> None:
+    """All ranks call this. One broadcast of image + header; receivers' module tensors (views of the blob) and integer
+    buffers hold the sender's values afterwards. Device-side only: no `.item()`, no host synchronisation."""
+    if dist.get_rank(group) == src:
+        flat.write_header(version)
+    dist.broadcast(flat.blob, src=src, group=group)
+    if dist.get_rank(group) != src:
+        flat.apply_header()
 
 
-def pack_image(state_dict, table, device) -> torch.Tensor:
-    parts = [state_dict[k].detach().to(device=device, dtype=torch.float32).reshape(-1) for k, _o, _n in float_table(state_dict, table)]
-    return torch.cat(parts) if parts else torch.empty(0, dtype=torch.float32, device=device)
+def received_version(flat: FlatWeights) -> tuple[int, int]:
+    """(version, image floats) as the sender wrote them; synchronises with the device (call it off the hot path)."""
+    h = flat.header[:2].cpu()
+    return int(h[0]), int(h[1])
 
 
-def unpack_image(image: torch.Tensor, table, state_dict) -> None:
-    """Copy the image back into the tensors of `state_dict` in place (keeps get_weights() truthful on receivers)."""
-    with torch.no_grad():
-        for key, off, numel in table:
-            t = state_dict[key]
-            t.copy_(image[off : off + numel].reshape(t.shape).to(device=t.device, dtype=t.dtype))
+class Publisher:
+    """Per-process state of overlapped weight publication: a side stream for the collective and the fold / repack."""
 
+    def __init__(self, nn, group=None):
+        self.nn = nn
+        self.group = group
+        self.stream = torch.cuda.Stream(device=nn.device)
+        self.done = torch.cuda.Event()
 
-def broadcast_state(state_dict, table, src: int, version: int, device, group=None):
-    """All ranks call this. Returns (image on `device`, version). Non-src ranks get their int buffers overwritten."""
-    rank = dist.get_rank(group)
-    ikeys = int_keys(state_dict)
-    total = sum(n for _k, _o, n in table)
-    header = torch.zeros(2 + len(ikeys), dtype=torch.int64, device=device)
-    if rank == src:
-        header[0] = version
-        header[1] = total
-        for i, k in enumerate(ikeys):
-            header[2 + i] = state_dict[k].reshape(-1)[0].to(torch.int64)
-        image = pack_image(state_dict, table, device)
-    else:
-        image = torch.empty(total, dtype=torch.float32, device=device)
-    dist.broadcast(header, src=src, group=group)
-    if int(header[1].item()) != total:
-        raise RuntimeError(f"weight image size mismatch: sender has {int(header[1].item())} floats, this rank expects {total}")
-    dist.broadcast(image, src=src, group=group)
-    if rank != src:
-        with torch.no_grad():
-            for i, k in enumerate(ikeys):
-                state_dict[k].fill_(int(header[2 + i].item()))
-    return image, int(header[0].item())
+    def publish(self, src: int = 0, version: int | None = None) -> None:
+        """Queue one publication and return. On the sender the side stream first waits for the work queued so far on the
+        current stream (the optimiser step that produced the weights); receivers' evaluations are not waited for and keep
+        reading their current set until the new one is ready."""
+        nn = self.nn
+        ver = nn._weights_version + 1 if version is None else int(version)
+        if dist.get_rank(self.group) == src:
+            self.stream.wait_stream(torch.cuda.current_stream(nn.device))
+        with torch.cuda.stream(self.stream):
+            broadcast_flat(nn.flat, src, ver, self.group)
+            nn._weights_version = ver
+            nn.engine.publish_image(nn.flat.image, ver)
+            nn._stamp = nn.flat.stamp()
+            self.done.record(self.stream)
+
+    def wait(self) -> None:
+        self.done.synchronize()
 
 
 def broadcast_weights(nn, src: int = 0, version: int | None = None, group=None) -> float:
-    """Publish rank `src`'s weights to every rank's engine. Returns this rank's elapsed milliseconds."""
+    """Publish rank `src`'s weights to every rank's engine on the current stream and wait. Returns this rank's elapsed
+    milliseconds (collective + fold / repack, device idle otherwise)."""
     dev = nn.device
     torch.cuda.synchronize(dev)
     t0 = time.perf_counter()
-    sd = nn._orig_model.state_dict()
-    ver = nn._weights_version + 1 if version is None else version
-    image, ver = broadcast_state(sd, nn.engine.table, src, ver, dev, group)
-    if dist.get_rank(group) != src:
-        unpack_image(image, nn.engine.table, sd)
-        nn._stamp = nn._module_stamp()
+    ver = nn._weights_version + 1 if version is None else int(version)
+    broadcast_flat(nn.flat, src, ver, group)
     nn._weights_version = ver
-    nn.engine.load_image(image, ver)
-    nn._stamp = nn._module_stamp()
+    nn.engine.load_image(nn.flat.image, ver)
+    nn._stamp = nn.flat.stamp()
     torch.cuda.synchronize(dev)
     return (time.perf_counter() - t0) * 1e3

@@ -75,25 +75,40 @@ class Engine:
 
     # ---- weights -------------------------------------------------------------------
     def build_image(self, state_dict: dict[str, torch.Tensor]) -> torch.Tensor:
-        """Concatenate the float tensors of a reference-keyed state_dict in engine order (on the device)."""
-        parts = []
-        for name, _off, numel in self.table:
+        """A weight image (device, fp32) from a reference-keyed state_dict: each float tensor at its table offset. For callers
+        that hold loose tensors; NeuralNetwork keeps its parameters inside such an image already (flat.py) and never packs."""
+        image = torch.zeros(self.image_floats, dtype=torch.float32, device=self.device)
+        for name, off, numel in self.table:
             if name not in state_dict:
                 raise KeyError(f"state_dict is missing {name!r}")
             t = state_dict[name]
             if t.numel() != numel:
                 raise ValueError(f"{name}: expected {numel} elements, got {tuple(t.shape)}")
-            parts.append(t.detach().to(device=self.device, dtype=torch.float32).reshape(-1))
-        return torch.cat(parts) if parts else torch.empty(0, device=self.device)
+            image[off : off + numel].copy_(t.detach().reshape(-1))
+        return image
 
-    def load_image(self, image: torch.Tensor, version: int = 0) -> None:
+    def _check_image(self, image: torch.Tensor) -> None:
         if image.device != self.device or image.dtype != torch.float32 or not image.is_contiguous():
             raise ValueError("weight image must be a contiguous float32 tensor on the engine's device")
+
+    def load_image(self, image: torch.Tensor, version: int = 0) -> None:
+        """Fold / repack `image` on the current stream; the next evaluate call reads the new set (it waits for the fold)."""
+        self._check_image(image)
         _lib.check(
             self.lib.at_engine_load_weights(self.handle, _ptr(image), image.numel(), int(version), _stream_ptr(self.device)),
             "at_engine_load_weights",
         )
         self._last_image = image  # keep alive until the fold kernels queued on the stream have read it
+
+    def publish_image(self, image: torch.Tensor, version: int = 0) -> None:
+        """Fold / repack `image` on the current stream (a side stream) while evaluations on other streams keep reading the
+        old set; they switch over at the first evaluate call after the fold has finished (at_engine_publish_weights)."""
+        self._check_image(image)
+        _lib.check(
+            self.lib.at_engine_publish_weights(self.handle, _ptr(image), image.numel(), int(version), _stream_ptr(self.device)),
+            "at_engine_publish_weights",
+        )
+        self._last_image = image
 
     def weight_version(self) -> int:
         return int(self.lib.at_engine_weight_version(self.handle))

@@ -19,6 +19,7 @@ import torch
 from . import _lib
 from .config import ModelConfig
 from .engine import Engine
+from .flat import FlatWeights
 from .net import AlphaTriangleNet
 from . import packing
 from .packing import RECORD_BYTES, pack_states
@@ -85,24 +86,33 @@ class NeuralNetwork:
         else:
             raise ValueError(f"precision must be 'auto', 'fp32' or 'bf16', got {precision!r}")
         self._action_keys = tuple(range(self.action_dim))
+        # parameters and float buffers become views into one flat buffer in the engine's image order (flat.py): in-place
+        # updates (optimiser steps, load_state_dict, an NCCL receive) write the engine's input directly
+        self.flat = FlatWeights(self._orig_model, self.engine.table, self.engine.image_floats, self.device)
         self._stamp: tuple | None = None
         self._weights_version = 0
         self._sync_engine()
 
     # ------------------------------------------------------------------ weights
     def _module_stamp(self) -> tuple:
-        sd = self._orig_model.state_dict(keep_vars=True)
-        return tuple((t.data_ptr(), t._version) for t in sd.values())
+        return self.flat.stamp()
 
     def _sync_engine(self, force: bool = False) -> None:
-        """Re-fold the module's tensors into the engine if they changed (trainer steps mutate them in place)."""
-        stamp = self._module_stamp()
+        """Re-fold the weights into the engine if any tensor was written since the last fold (trainer steps mutate them in
+        place; the check is the tensors' version counters, ~5 us). Anything that REPLACES parameter storage instead of
+        writing it (`model.to(...)`, `.half()`) must be followed by `refresh()`."""
+        stamp = self.flat.stamp()
         if not force and stamp == self._stamp:
             return
-        image = self.engine.build_image(self._orig_model.state_dict())
+        if not self.flat.aliased():
+            self.flat.adopt()
         self._weights_version += 1
-        self.engine.load_image(image, self._weights_version)
-        self._stamp = stamp
+        self.engine.load_image(self.flat.image, self._weights_version)
+        self._stamp = self.flat.stamp()
+
+    def refresh(self) -> None:
+        """Re-adopt the module's tensors into the flat buffer and re-fold, whatever happened to them."""
+        self._sync_engine(force=True)
 
     def get_weights(self) -> dict[str, torch.Tensor]:
         """state_dict of the underlying module, on the CPU (network.py:320-323)."""

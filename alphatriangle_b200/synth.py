@@ -141,17 +141,32 @@ def edge_states(env_config) -> list[SynthState]:
     ]
 
 
-def synth_state_dict(module_state_dict: dict, seed: int = 0) -> dict:
+def synth_state_dict(module_state_dict: dict, seed: int = 0, sharpness: float = 0.0) -> dict:
     """Deterministic weights for a reference-keyed state_dict, independent of torch's init order.
 
     Every float tensor is drawn from numpy's PCG64 in sorted-key order: weights ~ U(-a, a) with
     a = 1/sqrt(fan_in); BatchNorm running_mean ~ N(0, 0.1), running_var ~ U(0.5, 1.5), affine
     weight ~ U(0.8, 1.2), bias ~ N(0, 0.05) so that folding is really exercised; LayerNorm likewise.
     `pos_encoder.pe` and integer buffers are left as they are.
+
+    sharpness = 0 gives the small weights above: activations shrink with depth and the policy comes out
+    uniform to three digits (entropy ln 360 - 0.003), which says little about a trained network.
+    sharpness > 0 gives trained-like statistics instead: matrices ~ U(-a, a) with a = sqrt(6 / fan_in)
+    (variance-preserving through ReLU, so activations stay O(1) through the depth), and the last Linear of
+    the policy and value heads scaled by `sharpness`, which sets the spread of the logits: 2 gives policies
+    of 2-3 nats with a clear best move, 8 near-deterministic ones; expected values spread over the support.
     """
     import torch
 
     rng = np.random.default_rng(seed)
+    sharp = float(sharpness) > 0.0
+    last_linear = {}
+    if sharp:
+        for head in ("policy_head", "value_head"):
+            mats = sorted((int(k.split(".")[1]), k) for k, t in module_state_dict.items()
+                          if k.startswith(head + ".") and k.endswith(".weight") and t.dim() == 2)
+            if mats:
+                last_linear[mats[-1][1]] = float(sharpness)
     out = {}
     for key in sorted(module_state_dict):
         t = module_state_dict[key]
@@ -170,7 +185,7 @@ def synth_state_dict(module_state_dict: dict, seed: int = 0) -> dict:
             a = rng.normal(0.0, 0.05, shape)
         else:
             fan_in = int(np.prod(shape[1:]))
-            bound = 1.0 / np.sqrt(fan_in)
-            a = rng.uniform(-bound, bound, shape)
+            bound = np.sqrt(6.0 / fan_in) if sharp else 1.0 / np.sqrt(fan_in)
+            a = rng.uniform(-bound, bound, shape) * last_linear.get(key, 1.0)
         out[key] = torch.from_numpy(a.astype(np.float32)).to(t.device)
     return out

@@ -114,7 +114,10 @@ int at_engine_destroy(at_engine* e);
 /* The weight image is every floating-point tensor of the reference state_dict
  * (network.py:320-323) concatenated as fp32. The table below is the single
  * source of truth for its order: entry i is the reference key name (e.g.
- * "res_body.0.conv1.1.running_var"), its float offset and element count. */
+ * "res_body.0.conv1.1.running_var"), its float offset and element count. Offsets are
+ * multiples of 4 floats (a tensor whose size is not leaves up to three unused floats
+ * behind it), so a host can keep its parameters IN the image, as 16-byte-aligned views,
+ * and publish them without packing (alphatriangle_b200/flat.py). */
 int64_t at_engine_weight_floats(const at_engine* e);
 int at_engine_weight_entries(const at_engine* e);
 int at_engine_weight_entry(const at_engine* e, int index, const char** name, int64_t* offset, int64_t* numel);
@@ -126,6 +129,13 @@ int at_engine_weight_entry(const at_engine* e, int index, const char** name, int
  * work queued on `stream` completes. `version` is an opaque tag (the trainer's
  * global_step, worker_manager.py:184-187) returned by at_engine_weight_version. */
 int at_engine_load_weights(at_engine* e, const float* d_image, int64_t n_floats, int64_t version, void* stream);
+/* The same, for a worker that keeps evaluating while new weights arrive (the reference's workers go on playing while
+ * WorkerManager.update_worker_networks pushes, alphatriangle/training/worker_manager.py:169-209): the fold / repack is
+ * queued on `stream` -- typically the side stream the NCCL broadcast ran on -- into the inactive set, and evaluations on
+ * other streams keep reading the OLD set, without waiting, until that work has finished; the first evaluate call after
+ * that switches over. at_engine_weight_version reports the set evaluations currently read. An evaluation reads one set
+ * from start to end: never a mix. */
+int at_engine_publish_weights(at_engine* e, const float* d_image, int64_t n_floats, int64_t version, void* stream);
 int64_t at_engine_weight_version(const at_engine* e);
 
 /* 1 if the configuration can run on the tcgen05 bf16 path, else 0 (reason in at_last_error). */
@@ -175,7 +185,9 @@ int at_engine_evaluate_host(at_engine* e, int precision, const void* h_states, i
  * `slot` (0 or 1, each with its own device staging) and returns; wait blocks until that slot's probs / values / flags are
  * in the host buffers given at submit time. While slot 0's results drain over PCIe (5.9 MB per 4096 states) slot 1's
  * kernels run. A slot must be waited on before it is submitted to again; the host buffers must stay valid (and, for the
- * copies to be asynchronous, pinned) until the wait returns. The reference's evaluate_batch is synchronous
+ * copies to be asynchronous, pinned) until the wait returns. Both slots share the engine's tower -> FC hand-off scratch:
+ * submit both on the SAME `stream` (their kernels then run back to back; the overlap is between one slot's PCIe copies
+ * and the other slot's kernels). The reference's evaluate_batch is synchronous
  * (alphatriangle/nn/network.py:242-318); this pair is what a batcher serving many searches calls instead. */
 int at_engine_submit_host(at_engine* e, int precision, const void* h_states, int64_t batch, float* h_policy, float* h_value,
                           uint32_t* h_flags, int slot, void* stream);

@@ -4,13 +4,31 @@ from __future__ import annotations
 
 from alphatriangle_b200.synth import edge_states, synth_states
 
-CASES = ("default_tf", "conv_only", "ref_test_cfg", "odd_gelu", "strided_silu", "tanh_nobn", "sigmoid_tiny")
+# the two BASELINE models again with trained-like weights (synth_state_dict(sharpness=...)): "_sharp" policies of about two nats
+# with a clear best move on most states and expected values spread over the support, "_peaked" near-deterministic ones
+SHARP_CASES = ("conv_only_sharp", "conv_only_peaked", "default_tf_sharp", "default_tf_peaked")
+CASES = ("default_tf", "conv_only", "ref_test_cfg", "odd_gelu", "strided_silu", "tanh_nobn", "sigmoid_tiny") + SHARP_CASES
+_SHARPNESS = {"conv_only_sharp": 2.0, "conv_only_peaked": 8.0, "default_tf_sharp": 3.0, "default_tf_peaked": 8.0}
 
 _DIAMOND_4x5 = [(1, 4), (0, 5), (0, 5), (1, 4)]
 
 
+def case_sharpness(name: str) -> float:
+    return _SHARPNESS.get(name, 0.0)
+
+
+def case_weights(name: str, state_dict: dict) -> dict:
+    """The seeded weights of a case for a reference-keyed state_dict."""
+    from alphatriangle_b200.synth import synth_state_dict
+
+    return synth_state_dict(state_dict, case_configs(name)[2], case_sharpness(name))
+
+
 def case_configs(name: str):
     """-> (ModelConfig kwargs, EnvConfig kwargs, weight seed)"""
+    if name in _SHARPNESS:
+        mc_kwargs, env_kwargs, seed = case_configs(name.rsplit("_", 1)[0])
+        return mc_kwargs, env_kwargs, seed + 100
     if name == "default_tf":  # BASELINE config 1 / 3: the reference's defaults
         return {}, {}, 0
     if name == "conv_only":  # BASELINE config 2
@@ -62,5 +80,7 @@ def case_configs(name: str):
 
 
 def case_states(name: str, env_config):
+    if name in _SHARPNESS:  # same states as the base case: only the weights differ
+        return case_states(name.rsplit("_", 1)[0], env_config)
     n = 48 if name in ("default_tf", "conv_only") else 20
     return synth_states(n, env_config, seed=1234 + CASES.index(name)) + edge_states(env_config)

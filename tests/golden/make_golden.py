@@ -34,10 +34,9 @@ os.environ.setdefault("NUMBA_CACHE_DIR", "/tmp/numba_cache")
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
-from golden_cases import CASES, case_configs, case_states  # noqa: E402
+from golden_cases import CASES, case_configs, case_states, case_weights  # noqa: E402
 
 from alphatriangle_b200.packing import pack_states  # noqa: E402
-from alphatriangle_b200.synth import synth_state_dict  # noqa: E402
 
 
 def main() -> None:
@@ -65,7 +64,7 @@ def main() -> None:
         assert list(mine.keys()) == list(ref_sd.keys()), (name, set(mine) ^ set(ref_sd))
         for k in ref_sd:
             assert mine[k].shape == ref_sd[k].shape and mine[k].dtype == ref_sd[k].dtype, (name, k)
-        nn.set_weights(synth_state_dict(ref_sd, seed))
+        nn.set_weights(case_weights(name, ref_sd))
 
         feats = [ref_extract(s, ref_mc) for s in states]
         grid = np.stack([f["grid"] for f in feats])
@@ -93,8 +92,10 @@ def main() -> None:
             single_probs=np.array([single_pol[a] for a in range(action_dim)], dtype=np.float32),
             single_value=np.float32(single_val),
         )
+        entropy = -(probs * np.log(np.maximum(probs, 1e-30))).sum(axis=1)
         print(f"{name}: B={len(states)} grid{grid.shape} other{other.shape} probs{probs.shape} "
-              f"value[min,max]=[{values.min():.4f},{values.max():.4f}] keys={len(ref_sd)}")
+              f"value[min,max]=[{values.min():.4f},{values.max():.4f}] keys={len(ref_sd)} policy entropy mean {entropy.mean():.3f} "
+              f"nats, max prob > 0.3 on {(probs.max(axis=1) > 0.3).mean():.0%} of the states")
 
 
 if __name__ == "__main__":

@@ -2,10 +2,9 @@
 
 import numpy as np
 import torch
-from golden_cases import case_configs
+from golden_cases import case_configs, case_weights
 
 import alphatriangle_b200 as at
-from alphatriangle_b200.synth import synth_state_dict
 
 _NETS: dict = {}
 
@@ -22,7 +21,7 @@ def network(name, precision="fp32", max_batch=4096):
         mc_kwargs, env_kwargs, seed = case_configs(name)
         mc, env = at.ModelConfig(**mc_kwargs), at.EnvConfig(**env_kwargs)
         nn = at.NeuralNetwork(mc, env, at.TrainConfig(), torch.device("cuda:0"), precision=precision, max_batch=max_batch)
-        nn.set_weights(synth_state_dict(nn.get_weights(), seed))
+        nn.set_weights(case_weights(name, nn.get_weights()))
         _NETS[key] = nn
     return _NETS[key]
 

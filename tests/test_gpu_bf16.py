@@ -14,8 +14,24 @@ from oracle import features_ref, model_ref
 pytestmark = pytest.mark.gpu
 
 KL_TOL = 1e-3      # north_star: policy KL(reference || ours) per state, bf16 path
-VALUE_TOL = 5e-2   # expected value, |ours - reference|; support spans [-10, 10], bf16 operands (8-bit mantissa)
 TRUNK_TOL = 3e-2   # first shared-FC activation, relative to its largest magnitude
+
+# Expected value, |ours - reference| on the [-10, 10] support. bf16 operands carry an 8-bit mantissa: every operand is off by
+# up to 2^-9 relative, which through the tower, the trunk FC and the heads comes to ~0.5 % rms on a logit, so the error of
+# E[z] grows with the spread of the value logits. Measured on the B200 / bound asserted here:
+#   small-weight cases (logit sigma ~0.1, values within +-0.06):   2-8e-4  / 5e-3
+#   trained-like "_sharp" cases (value logit sigma ~6):            see DESIGN.md / 0.6
+#   near-deterministic "_peaked" cases (value logit sigma ~20):    see DESIGN.md / 1.2
+VALUE_TOL = {"plain": 5e-3, "sharp": 0.6, "peaked": 1.2}
+# Policy KL: the north_star bound holds up to the "_sharp" cases (policies of about two nats). The "_peaked" cases (logit sigma
+# 10-18, entropy 0.4-0.6 nats) are outside what 8-bit mantissas can hold to 1e-3 -- KL ~ (logit error)^2 / 2 and the logit
+# error scales with the logits -- so they are bounded at what was measured with margin, and DESIGN.md says so.
+KL_TOL_BY_KIND = {"plain": KL_TOL, "sharp": KL_TOL, "peaked": 2e-2}
+
+
+def kind_of(case):
+    return case.rsplit("_", 1)[-1] if case.endswith(("_sharp", "_peaked")) else "plain"
+
 
 
 def test_bf16_path_is_available_for_the_baseline_config():
@@ -29,6 +45,7 @@ def test_bf16_path_is_available_for_the_baseline_config():
 
 
 BF16_CASES = ["conv_only", "default_tf"]  # BASELINE configs 2 and 3: conv tower alone / fused with the encoder layers
+GOLDEN_CASES = BF16_CASES + ["conv_only_sharp", "conv_only_peaked", "default_tf_sharp", "default_tf_peaked"]
 
 
 @pytest.mark.parametrize("case", BF16_CASES)
@@ -43,15 +60,22 @@ def test_trunk_activation_matches_oracle(case, golden_dir):
     assert np.abs(got - ref).max() <= TRUNK_TOL * scale, (np.abs(got - ref).max(), scale)
 
 
-@pytest.mark.parametrize("case", BF16_CASES)
-def test_bf16_matches_reference_golden(case, golden_dir):
+@pytest.mark.parametrize("case", GOLDEN_CASES)
+def test_bf16_matches_reference_golden(case, golden_dir, record_property):
     mc, env, _seed, g = load_case(case, golden_dir)
     nn = network(case, "bf16")
     probs, value = nn.evaluate_packed(torch.from_numpy(g["packed"]).cuda())
     probs, value = probs.cpu().numpy(), value.cpu().numpy()
-    assert kl_rows(g["probs"], probs).max() <= KL_TOL
-    assert np.abs(value - g["values"]).max() <= VALUE_TOL
+    kl = kl_rows(g["probs"], probs)
+    verr = np.abs(value - g["values"])
+    agree = float((probs.argmax(axis=1) == g["probs"].argmax(axis=1)).mean())
+    print(f"[bf16 parity] {case}: policy KL max {kl.max():.3e} mean {kl.mean():.3e}; value |err| max {verr.max():.3e} "
+          f"mean {verr.mean():.3e}; best move agrees on {agree:.1%}")
+    assert kl.max() <= KL_TOL_BY_KIND[kind_of(case)]
+    assert verr.max() <= VALUE_TOL[kind_of(case)]
     assert np.abs(probs.sum(axis=1) - 1.0).max() < 1e-5
+    if kind_of(case) != "plain":  # the move a search would rank first is the reference's (ties aside)
+        assert agree >= 0.95
 
 
 @pytest.mark.parametrize("case", BF16_CASES)
@@ -66,7 +90,7 @@ def test_bf16_ragged_batches_match_oracle(case, batch, golden_dir):
     p_ref, v_ref = model_ref.evaluate_tensors(nn.get_weights(), mc, grid, other)
     probs, value = nn.evaluate_packed(torch.from_numpy(pack_states(states, env)).cuda())
     assert kl_rows(p_ref, probs.cpu().numpy()).max() <= KL_TOL
-    assert np.abs(value.cpu().numpy() - v_ref).max() <= VALUE_TOL
+    assert np.abs(value.cpu().numpy() - v_ref).max() <= VALUE_TOL["plain"]
 
 
 @pytest.mark.parametrize("case", BF16_CASES)
@@ -103,6 +127,45 @@ def test_bf16_through_the_drop_in_api(golden_dir):
         row = np.array([pol[a] for a in range(nn.action_dim)])
         assert abs(row.sum() - 1.0) < 1e-5
         assert kl_rows(g["probs"][i : i + 1], row[None, :]).max() <= KL_TOL
-        assert abs(val - float(g["values"][i])) <= VALUE_TOL
+        assert abs(val - float(g["values"][i])) <= VALUE_TOL["plain"]
     t = nn.engine.kernel_times()
     assert t is not None and t["tower_ms"] > 0 and t["fc_ms"] > 0
+
+
+# Head shapes that leave the tensor-core head kernel: (ModelConfig overrides, kernels expected after the tower and the FC)
+HEAD_SHAPES = {
+    # hidden widths differ from the trunk's -> heads_fused_kernel (same fusion on CUDA cores, fp32)
+    "cuda_core_heads": (dict(USE_TRANSFORMER=False, FC_DIMS_SHARED=[128], POLICY_HEAD_DIMS=[64], VALUE_HEAD_DIMS=[32]), 4),
+    # two shared layers, a two-layer policy head and a value head without hidden layer -> the unfused tail
+    # (split-K finish, one GEMM per layer, softmax kernel, status merge)
+    "unfused_tail": (dict(USE_TRANSFORMER=False, FC_DIMS_SHARED=[128, 64], POLICY_HEAD_DIMS=[64, 32], VALUE_HEAD_DIMS=[]), None),
+    # the same two with the encoder layers in front
+    "cuda_core_heads_tf": (dict(FC_DIMS_SHARED=[96], POLICY_HEAD_DIMS=[48], VALUE_HEAD_DIMS=[24]), 4),
+}
+
+
+@pytest.mark.parametrize("shape", sorted(HEAD_SHAPES))
+def test_bf16_other_head_kernels_match_oracle(shape):
+    """Every CUDA path that ships gets launched: head shapes outside heads_mma_kernel's specialisation."""
+    import alphatriangle_b200 as at
+    from alphatriangle_b200.synth import synth_state_dict
+
+    overrides, want_launches = HEAD_SHAPES[shape]
+    mc, env = at.ModelConfig(**overrides), at.EnvConfig()
+    nn = at.NeuralNetwork(mc, env, None, torch.device("cuda:0"), precision="bf16", max_batch=256)
+    nn.set_weights(synth_state_dict(nn.get_weights(), 77, sharpness=1.0))
+    states = synth_states(150, env, seed=4321) + edge_states(env)
+    grid, other = features_ref.extract_batch(states, mc)
+    p_ref, v_ref = model_ref.evaluate_tensors(nn.get_weights(), mc, grid, other)
+    probs, value = nn.evaluate_packed(torch.from_numpy(pack_states(states, env)).cuda())
+    launches = nn.engine.last_launches()
+    if want_launches is None:
+        assert launches > 6, launches
+    else:
+        assert launches == want_launches, launches  # features, tower, FC, one head kernel
+    kl = kl_rows(p_ref, probs.cpu().numpy())
+    verr = np.abs(value.cpu().numpy() - v_ref)
+    print(f"[bf16 parity] {shape}: policy KL max {kl.max():.3e}; value |err| max {verr.max():.3e}; {launches} launches")
+    assert kl.max() <= KL_TOL
+    assert verr.max() <= 0.3
+    assert np.abs(probs.cpu().numpy().sum(axis=1) - 1.0).max() < 1e-5

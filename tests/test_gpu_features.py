@@ -66,3 +66,32 @@ def test_features_full_size_properties(batch):
     assert set(np.unique(grid)) <= {-1.0, 0.0, 1.0}
     assert other[:, :24].min() >= 0.0 and other[:, :24].max() <= 1.0
     assert np.abs(other[:, 24]).max() <= 5.0 and np.isfinite(other).all()
+
+
+@pytest.mark.parametrize("rows,cols,ranges", [
+    (3, 40, [(2, 38), (0, 40), (1, 39)]),      # 120 cells, columns straddle a 32-bit word
+    (2, 64, [(0, 64), (5, 60)]),               # 128 cells: the record's limit
+    (1, 33, [(0, 33)]),                        # one row, just past the fast kernel's 32 columns
+])
+def test_wide_boards_take_the_generic_kernel_bit_exact(rows, cols, ranges):
+    """Boards wider than 32 columns run features_kernel (16 lanes per state over the columns, fp64 arithmetic) instead of
+    the bit-parallel features_fast_kernel. Same bit-exact bar, against the numpy oracle and its plain-C twin."""
+    import ctypes as C
+    from pathlib import Path
+
+    from alphatriangle_b200.features import _run
+
+    env = at.EnvConfig(ROWS=rows, COLS=cols, PLAYABLE_RANGE_PER_ROW=ranges, NUM_SHAPE_SLOTS=4)
+    for channels, dim in ((1, 38), (2, 45), (1, 7)):
+        mc = at.ModelConfig(GRID_INPUT_CHANNELS=channels, OTHER_NN_INPUT_FEATURES_DIM=dim)
+        states = synth_states(333, env, seed=17 + cols) + edge_states(env)
+        packed = pack_states(states, env)
+        grid, other = _run(packed, env, channels, dim, torch.device("cuda:0"))
+        g0, o0 = features_ref.extract_batch(states, mc)
+        assert np.array_equal(bits(grid), bits(g0))
+        assert np.array_equal(bits(other), bits(o0))
+        lib = C.CDLL(str(Path(__file__).resolve().parents[1] / "oracle" / "liboracle_features.so"))
+        gc, oc = np.empty_like(g0), np.empty_like(o0)
+        assert lib.at_oracle_features(C.c_void_p(packed.ctypes.data), C.c_int64(len(states)), rows, cols, 4, channels, dim,
+                                      C.c_void_p(gc.ctypes.data), C.c_void_p(oc.ctypes.data)) == 0
+        assert np.array_equal(bits(grid), bits(gc)) and np.array_equal(bits(other), bits(oc))

@@ -5,11 +5,10 @@ restated forward must agree with the reference's module forward to fp32 round-of
 import numpy as np
 import pytest
 import torch
-from golden_cases import CASES, case_configs, case_states
+from golden_cases import CASES, case_configs, case_states, case_weights
 
 import alphatriangle_b200 as at
 from alphatriangle_b200.packing import pack_states
-from alphatriangle_b200.synth import synth_state_dict
 from oracle import features_ref, model_ref
 
 
@@ -45,19 +44,22 @@ def test_feature_oracle_bit_exact(name, golden_dir):
 def test_forward_oracle_matches_reference(name, golden_dir):
     mc, env, seed, g = _load(name, golden_dir)
     torch.set_num_threads(1)
-    sd = synth_state_dict(at.AlphaTriangleNet(mc, env).state_dict(), seed)
+    sd = case_weights(name, at.AlphaTriangleNet(mc, env).state_dict())
     pl, vl = model_ref.forward(sd, mc, torch.from_numpy(g["grid"]), torch.from_numpy(g["other"]))
-    assert np.abs(pl.numpy() - g["policy_logits"]).max() < 2e-5
-    assert np.abs(vl.numpy() - g["value_logits"]).max() < 2e-5
+    # fp32 summation order differs between the module tree and the functional restatement: the round-off scales with
+    # the logits, which are O(0.1) with the small weights and O(10-50) with the trained-like ones
+    scale = max(1.0, float(np.abs(g["policy_logits"]).max()), float(np.abs(g["value_logits"]).max()))
+    assert np.abs(pl.numpy() - g["policy_logits"]).max() < 2e-5 * scale
+    assert np.abs(vl.numpy() - g["value_logits"]).max() < 2e-5 * scale
     probs, values = model_ref.evaluate_tensors(sd, mc, g["grid"], g["other"])
-    assert np.abs(probs - g["probs"]).max() < 1e-6
-    assert np.abs(values - g["values"]).max() < 1e-5
+    assert np.abs(probs - g["probs"]).max() < 1e-6 * scale
+    assert np.abs(values - g["values"]).max() < 1e-5 * scale
 
 
 @pytest.mark.parametrize("name", ["ref_test_cfg", "odd_gelu"])
 def test_evaluate_batch_oracle_structure(name, golden_dir):
     mc, env, seed, g = _load(name, golden_dir)
-    sd = synth_state_dict(at.AlphaTriangleNet(mc, env).state_dict(), seed)
+    sd = case_weights(name, at.AlphaTriangleNet(mc, env).state_dict())
     states = case_states(name, env)
     res = model_ref.evaluate_batch(sd, mc, states)
     assert len(res) == len(states)
