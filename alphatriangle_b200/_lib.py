@@ -20,7 +20,9 @@ FLAG_NONFINITE_VALUE_LOGITS = 8
 FLAG_NONFINITE_POLICY_PROBS = 16
 FLAG_PIPELINE_TIMEOUT = 0x80000000
 
-PREC_FP32, PREC_BF16 = 0, 1
+PREC_FP32, PREC_BF16, PREC_F16 = 0, 1, 2
+TENSOR_CORE_PRECISIONS = (PREC_BF16, PREC_F16)
+PRECISION_NAMES = {PREC_FP32: "fp32", PREC_BF16: "bf16", PREC_F16: "f16"}
 STATE_BYTES = 80
 MAX_CONVS, MAX_MLP = 8, 4
 

@@ -29,6 +29,7 @@
 
 #include "at_bf16.cuh"
 #include "at_fp32.cuh"
+#include "at_prepjobs.cuh"
 #include "at_umma.cuh"
 
 namespace at {
@@ -105,7 +106,18 @@ __device__ __forceinline__ bool elect_one() {
   return pred != 0;
 }
 
+// Wait for an mbarrier phase. A wedged pipeline reports through `status` instead of hanging the GPU (after ~1 s).
+// Mode 0 (shipped): plain try_wait in a loop. A waiting warp then re-issues ~9 instructions every ~65 cycles -- two thirds of
+// all warp instructions tower_kernel executes are this loop (ncu source view, profiles/r02_wait_loop.txt) -- yet parking the
+// warp instead (mode 1: try_wait with a suspend-time hint, no clock reads) was measured 1-2 % SLOWER on both tower kernels:
+// what matters is how fast the waiter wakes, not the issue slots it burns meanwhile.
+#ifndef AT_WAIT_MODE
+#define AT_WAIT_MODE 0
+#endif
+constexpr uint32_t kWaitHintNs = 1u << 20;
+constexpr uint32_t kWaitTries = 1u << 20;  // the hardware caps a single suspension well below the hint: bound by count, not by clock
 __device__ __forceinline__ bool wait_bar(uint32_t bar, uint32_t parity, uint32_t* status, uint32_t code) {
+#if AT_WAIT_MODE == 0
   if (mbar_try_wait(bar, parity)) return true;  // common case: no clock reads on the fast path
   const long long t0 = clock64();
   while (!mbar_try_wait(bar, parity)) {
@@ -115,36 +127,67 @@ __device__ __forceinline__ bool wait_bar(uint32_t bar, uint32_t parity, uint32_t
     }
   }
   return true;
+#else
+  if (mbar_try_wait_hint(bar, parity, kWaitHintNs)) return true;
+  for (uint32_t tries = 0; tries < kWaitTries; ++tries)
+    if (mbar_try_wait_hint(bar, parity, kWaitHintNs)) return true;
+  atomicOr(status, code);
+  return false;
+#endif
 }
 
-__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
-  __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
-  return *reinterpret_cast<uint32_t*>(&v);
+// ---- 16-bit operand formats (FMT_BF16 / FMT_F16, at_prepjobs.cuh). Activations are rounded to the operand format once,
+// where an epilogue hands them to the next MMA; fp16 conversions saturate at +-65504 instead of producing infinities.
+template <int FMT>
+__device__ __forceinline__ uint32_t pack2(float lo, float hi) {
+  uint32_t w;
+  if constexpr (FMT == FMT_F16) asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(w) : "f"(hi), "f"(lo));
+  else asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w) : "f"(hi), "f"(lo));
+  return w;
 }
-__device__ __forceinline__ float bf16_lo(uint32_t w) { return __uint_as_float(w << 16); }
-__device__ __forceinline__ float bf16_hi(uint32_t w) { return __uint_as_float(w & 0xFFFF0000u); }
+// the same with the ReLU clamp built into the conversion (negative and NaN inputs give +0)
+template <int FMT>
+__device__ __forceinline__ uint32_t pack2_relu(float lo, float hi) {
+  uint32_t w;
+  if constexpr (FMT == FMT_F16) asm("cvt.rn.relu.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(w) : "f"(hi), "f"(lo));
+  else asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(w) : "f"(hi), "f"(lo));
+  return w;
+}
+template <int FMT>
+__device__ __forceinline__ void unpack2(uint32_t w, float& lo, float& hi) {
+  if constexpr (FMT == FMT_F16) {
+    asm("{.reg .f16 l, h; mov.b32 {l, h}, %2; cvt.f32.f16 %0, l; cvt.f32.f16 %1, h;}" : "=f"(lo), "=f"(hi) : "r"(w));
+  } else {
+    lo = __uint_as_float(w << 16);
+    hi = __uint_as_float(w & 0xFFFF0000u);
+  }
+}
 
 template <int ACT>
 __device__ __forceinline__ float act_fn(float x) {
   if constexpr (ACT == AT_ACT_RELU) return fmaxf(x, 0.0f);
   else return apply_act(x, ACT);
 }
-// eight fp32 values -> activation -> bf16, zeroed when `keep` is 0 (padding rows). ReLU rides on the conversion
-// (cvt.rn.relu.bf16x2.f32) and the row mask is a single AND per pair.
-template <int ACT>
+template <int ACT, int FMT>
+__device__ __forceinline__ uint32_t pack2_act(float lo, float hi) {
+  if constexpr (ACT == AT_ACT_RELU) return pack2_relu<FMT>(lo, hi);
+  else return pack2<FMT>(act_fn<ACT>(lo), act_fn<ACT>(hi));
+}
+// eight fp32 values -> activation -> 16-bit operands, zeroed when `keep` is 0 (padding rows): one conversion per pair (the
+// ReLU rides on it) and a single AND for the row mask.
+template <int ACT, int FMT>
 __device__ __forceinline__ uint4 pack8_act(const float (&v)[8], uint32_t keep) {
-  uint32_t w[4];
-#pragma unroll
-  for (int i = 0; i < 4; ++i) {
-    if constexpr (ACT == AT_ACT_RELU) {
-      uint32_t h;  // round-to-nearest conversion with the ReLU clamp built in (negative and NaN inputs give +0)
-      asm("cvt.rn.relu.bf16x2.f32 %0, %1, %2;" : "=r"(h) : "f"(v[2 * i + 1]), "f"(v[2 * i]));
-      w[i] = h & keep;
-    } else {
-      w[i] = pack_bf16x2(act_fn<ACT>(v[2 * i]), act_fn<ACT>(v[2 * i + 1])) & keep;
-    }
-  }
-  return make_uint4(w[0], w[1], w[2], w[3]);
+  return make_uint4(pack2_act<ACT, FMT>(v[0], v[1]) & keep, pack2_act<ACT, FMT>(v[2], v[3]) & keep,
+                    pack2_act<ACT, FMT>(v[4], v[5]) & keep, pack2_act<ACT, FMT>(v[6], v[7]) & keep);
+}
+// v[0..7] += the eight 16-bit values of `w`
+template <int FMT>
+__device__ __forceinline__ void add8(float (&v)[8], const uint4& w) {
+  float lo, hi;
+  unpack2<FMT>(w.x, lo, hi); v[0] += lo; v[1] += hi;
+  unpack2<FMT>(w.y, lo, hi); v[2] += lo; v[3] += hi;
+  unpack2<FMT>(w.z, lo, hi); v[4] += lo; v[5] += hi;
+  unpack2<FMT>(w.w, lo, hi); v[6] += lo; v[7] += hi;
 }
 
 __device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
@@ -196,7 +239,7 @@ __device__ __forceinline__ void issue_slab1(uint32_t tmem_d, uint32_t a16, uint3
 //  * tried and dropped: CTA pairs with cta_group::2, an 8 x 8 KB ring, two issuing warps per board (no gain, and the
 //    accumulation order -- hence the low bits -- then depends on timing), two accumulators per board with a channel-half
 //    hand-off (overlap gain smaller than the added per-slab instructions).
-template <int ACT>
+template <int ACT, int FMT>
 __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_constant__ TowerParams p) {
   constexpr int NS = kStages;
   constexpr uint32_t SB = kStageBytes;
@@ -291,7 +334,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         if (!ok) break;
         lphase ^= 1u;
         tc_fence_after();
-        const uint32_t idesc = idesc_bf16(kM, (uint32_t)L.cout);
+        const uint32_t idesc = idesc_16(kM, (uint32_t)L.cout, FMT == FMT_BF16);
         // descriptor low words: [13:0] start address >> 4, [29:16] LBO >> 4; the address sums below stay inside 14 bits
         const uint32_t a_base = a_lo_fixed | ((act_u + (uint32_t)(me * 2 + L.src) * kBufBytes) >> 4);
         const uint32_t b_base = ((uint32_t)L.cout << 16) | (ring_u >> 4);  // LBO = one 8-channel plane of the slab (Cout rows of 16 B)
@@ -382,7 +425,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
             v[0] = fmaf(g[t], wa.x, v[0]); v[1] = fmaf(g[t], wa.y, v[1]); v[2] = fmaf(g[t], wa.z, v[2]); v[3] = fmaf(g[t], wa.w, v[3]);
             v[4] = fmaf(g[t], wb.x, v[4]); v[5] = fmaf(g[t], wb.y, v[5]); v[6] = fmaf(g[t], wb.z, v[6]); v[7] = fmaf(g[t], wb.w, v[7]);
           }
-          sts128(my_act_u + (uint32_t)(c8 / 8) * kPlaneBytes, pack8_act<ACT>(v, keep));
+          sts128(my_act_u + (uint32_t)(c8 / 8) * kPlaneBytes, pack8_act<ACT, FMT>(v, keep));
         }
       }
       arrive_act();
@@ -416,11 +459,9 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
                             __uint_as_float(r[i * 8 + 6]) + bb.z, __uint_as_float(r[i * 8 + 7]) + bb.w};
               const int chunk = c0 / 8 + i;
               if constexpr (decltype(HAS_RES)::value) {
-                const uint4 rv = lds128(res_u + (uint32_t)chunk * kPlaneBytes);
-                v[0] += bf16_lo(rv.x); v[1] += bf16_hi(rv.x); v[2] += bf16_lo(rv.y); v[3] += bf16_hi(rv.y);
-                v[4] += bf16_lo(rv.z); v[5] += bf16_hi(rv.z); v[6] += bf16_lo(rv.w); v[7] += bf16_hi(rv.w);
+                add8<FMT>(v, lds128(res_u + (uint32_t)chunk * kPlaneBytes));
               }
-              const uint4 out = pack8_act<ACT>(v, keep);
+              const uint4 out = pack8_act<ACT, FMT>(v, keep);
               if constexpr (decltype(TO_SMEM)::value) {
                 sts128(dst_u + (uint32_t)chunk * kPlaneBytes, out);
               } else {
@@ -460,6 +501,7 @@ struct FcParams {
   int64_t batch;
   int n_kc, N, slabs_per_split, n_slabs;
   uint32_t* status;
+  int fmt;  // operand format of a and w (FMT_BF16 / FMT_F16)
 };
 
 constexpr size_t fc_smem_bytes() { return (size_t)kFcStages * 2 * kStageBytes + (2 * kFcStages + 1) * 8 + 16; }
@@ -512,7 +554,7 @@ __global__ void __launch_bounds__(kFcThreads, 2) fc_kernel(const __grid_constant
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      const uint32_t idesc = idesc_bf16(kM, (uint32_t)p.N);
+      const uint32_t idesc = idesc_16(kM, (uint32_t)p.N, p.fmt == FMT_BF16);
       const uint32_t b_lbo = (uint32_t)p.N * 16;
       bool ok = true;
       for (int s = s_begin; s < s_end; ++s) {
@@ -561,29 +603,11 @@ __global__ void __launch_bounds__(kFcThreads, 2) fc_kernel(const __grid_constant
   if (warp == 0) tmem_dealloc(tmem_base, cols);
 }
 
-// fp32 [K,N] (row k contiguous in n) -> bf16 core-matrix tiles [K/8][N][8]
-__global__ void __launch_bounds__(256) pack_b_kernel(const float* __restrict__ wt, int K, int N, __nv_bfloat16* __restrict__ dst) {
-  const int64_t total = (int64_t)K * N;
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t kc = i / ((int64_t)N * 8);
-    const int rem = (int)(i - kc * N * 8);
-    const int n = rem / 8, e = rem % 8;
-    dst[i] = __float2bfloat16_rn(wt[(kc * 8 + e) * N + n]);
-  }
-}
-
-__global__ void gather_bias_kernel(const float* __restrict__ folded, const int64_t* __restrict__ offs, const int* __restrict__ widths,
-                                   int n_layers, float* __restrict__ dst) {
-  const int l = blockIdx.x;
-  if (l >= n_layers) return;
-  for (int i = threadIdx.x; i < 128; i += blockDim.x) dst[l * 128 + i] = i < widths[l] ? folded[offs[l] + i] : 0.0f;
-}
-
 #include "at_bf16_tf.inc"
 
 constexpr size_t tower_tf_smem_bytes() {
-  return (size_t)kTfStages * kStageBytes + (size_t)kBoards * 2 * kBufBytes + (size_t)kMaxLayers * 128 * 4 + 9 * 128 * 4 + 128 * 4 +
-         (size_t)kXchFloats * 4 + (2 * kStages + 4) * 8 + 16;
+  return (size_t)kTfStages * kStageBytes + (size_t)kBoards * 2 * kBufBytes + kMaskBytes + (size_t)kMaxLayers * 128 * 4 + 9 * 128 * 4 +
+         128 * 4 + (size_t)kXchFloats * 4 + (2 * kStages + 4) * 8 + 16;
 }
 
 }  // namespace
@@ -602,8 +626,6 @@ struct Bf16Path {
   uint8_t* wstream[2] = {nullptr, nullptr};
   uint8_t* wfc[2] = {nullptr, nullptr};
   float* bias[2] = {nullptr, nullptr};
-  int64_t* d_bias_off = nullptr;
-  int* d_bias_w = nullptr;
   // trunk FC
   int fc_n = 0, fc_flat = 0, n_kc = 0;
   int64_t fc_wt = 0;
@@ -621,9 +643,10 @@ struct Bf16Path {
   // transformer extension (tower_tf_kernel)
   bool tf = false;
   TowerTfParams ttp{};
-  float* tfp[2] = {nullptr, nullptr};
-  int tfp_floats = 0;
+  float* fc_bias[2] = {nullptr, nullptr};  // trunk FC bias with the encoder's final LayerNorm folded in (fp32 [fc_n])
+  int64_t fc_bias_off = 0;                  // the plain bias in the folded set
   size_t conv_stream_bytes = 0;
+  int packed_fmt[2] = {-1, -1};             // operand format the 16-bit images of each weight set currently hold
 };
 
 int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* reason) {
@@ -740,33 +763,35 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
       if (n < kMaxRingSlabs) t.slab16[n] = (uint16_t)(bytes / 16);
       ++n;
     };
+    auto bias_slab = [&](int N) { slab(2u * (uint32_t)N * 16u); };  // two 8-wide K planes, row 0 = the bias
     for (int l = 0; l < tp.n_layers; ++l)
       for (int sl = 0; sl < tp.layers[l].n_slabs; ++sl) slab(tp.layers[l].slab_bytes);
-    int off = 0;
-    auto take = [&](int count) {
-      const int at0 = off;
-      off += (count + 3) & ~3;
-      return at0;
-    };
+    // the encoder's slabs in the order the issuers consume them (tower_tf_kernel, "encoder layers")
     for (int l = 0; l < d.t_layers; ++l) {
       for (int h = 0; h < d.t_heads; ++h) {
-        if (h > 0) slab(kTfD * kTfDh * 2);                    // out_proj columns of head h-1
+        if (h > 0) {
+          slab(kTfD * kTfDh * 2);                             // out_proj columns of head h-1
+          if (h == 1) bias_slab(kTfD);                        // out_proj bias
+        }
         slab(3 * kTfDh * 64 * 2); slab(3 * kTfDh * 64 * 2);   // fused q|k|v projection of head h, two K halves
+        bias_slab(3 * kTfDh);
       }
       slab(kTfD * kTfDh * 2);
+      if (d.t_heads == 1) bias_slab(kTfD);
       for (int f = 0; f < t.ff_halves; ++f) {
-        if (f > 0) { slab(128 * 64 * 2); slab(128 * 64 * 2); }  // linear2, hidden half f-1
-        slab(128 * 64 * 2); slab(128 * 64 * 2);                 // linear1, hidden half f
+        if (f > 0) {
+          slab(128 * 64 * 2); slab(128 * 64 * 2);             // linear2, hidden half f-1
+          if (f == 1) bias_slab(kTfD);                        // linear2 bias
+        }
+        slab(128 * 64 * 2); slab(128 * 64 * 2);               // linear1, hidden half f
+        bias_slab(128);
       }
       slab(128 * 64 * 2); slab(128 * 64 * 2);
-      b->wstream_bytes += (size_t)d.t_heads * (3 * kTfDh * kTfD + kTfD * kTfDh) * 2 + (size_t)t.ff_halves * 2 * 128 * 128 * 2;
-      TfLayerOffsets& o = t.tl[l];
-      o.ln1_w = take(kTfD); o.ln1_b = take(kTfD); o.bq = take(kTfD); o.bk = take(kTfD); o.bv = take(kTfD); o.bout = take(kTfD);
-      o.ln2_w = take(kTfD); o.ln2_b = take(kTfD); o.b1 = take(d.t_ff); o.b2 = take(kTfD);
+      if (t.ff_halves == 1) bias_slab(kTfD);
     }
-    t.lnf_w = take(kTfD);
-    t.lnf_b = take(kTfD);
-    b->tfp_floats = off;
+    b->wstream_bytes = 0;
+    for (int i = 0; i < n && i < kMaxRingSlabs; ++i) b->wstream_bytes += (size_t)t.slab16[i] * 16;
+    b->fc_bias_off = fc.bias;
     t.n_ring_slabs = n;
     if (n > kMaxRingSlabs) {
       delete b;
@@ -788,13 +813,14 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
       AT_CUDA_TRY(cudaMalloc(&b->bias[i], (size_t)kMaxLayers * 128 * sizeof(float)));
     }
     if (b->tf)
-      for (int i = 0; i < 2; ++i) AT_CUDA_TRY(cudaMalloc(&b->tfp[i], (size_t)b->tfp_floats * sizeof(float)));
-    AT_CUDA_TRY(cudaFuncSetAttribute(tower_tf_kernel<AT_ACT_RELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_tf_smem_bytes()));
-    AT_CUDA_TRY(cudaFuncSetAttribute(tower_tf_kernel<AT_ACT_GELU>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_tf_smem_bytes()));
-    AT_CUDA_TRY(cudaMalloc(&b->d_bias_off, kMaxLayers * sizeof(int64_t)));
-    AT_CUDA_TRY(cudaMalloc(&b->d_bias_w, kMaxLayers * sizeof(int)));
-    AT_CUDA_TRY(cudaMemcpy(b->d_bias_off, b->bias_off.data(), b->bias_off.size() * sizeof(int64_t), cudaMemcpyHostToDevice));
-    AT_CUDA_TRY(cudaMemcpy(b->d_bias_w, b->bias_w.data(), b->bias_w.size() * sizeof(int), cudaMemcpyHostToDevice));
+      for (int i = 0; i < 2; ++i) AT_CUDA_TRY(cudaMalloc(&b->fc_bias[i], (size_t)fc.N * sizeof(float)));
+#define AT_TF_ATTR(ACT_, FMT_) \
+  AT_CUDA_TRY(cudaFuncSetAttribute(tower_tf_kernel<ACT_, FMT_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_tf_smem_bytes()));
+    AT_TF_ATTR(AT_ACT_RELU, FMT_BF16)
+    AT_TF_ATTR(AT_ACT_RELU, FMT_F16)
+    AT_TF_ATTR(AT_ACT_GELU, FMT_BF16)
+    AT_TF_ATTR(AT_ACT_GELU, FMT_F16)
+#undef AT_TF_ATTR
     AT_CUDA_TRY(cudaMalloc(&b->fc_a, (size_t)m_tiles * b->n_kc * 2048));
     AT_CUDA_TRY(cudaMemset(b->fc_a, 0, (size_t)m_tiles * b->n_kc * 2048));
     AT_CUDA_TRY(cudaMalloc(&b->partial, (size_t)(b->max_splits + 1) * max_batch * fc.N * sizeof(float)));
@@ -804,7 +830,8 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
     AT_CUDA_TRY(cudaMemset(b->status, 0, 4 * sizeof(uint32_t)));
     for (auto& e : b->ev) AT_CUDA_TRY(cudaEventCreate(&e));
 #define AT_TOWER_ATTR(ACT_) \
-  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
+  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, FMT_BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes())); \
+  AT_CUDA_TRY(cudaFuncSetAttribute(tower_kernel<ACT_, FMT_F16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)tower_smem_bytes()));
     AT_TOWER_ATTR(AT_ACT_RELU)
     AT_TOWER_ATTR(AT_ACT_GELU)
     AT_TOWER_ATTR(AT_ACT_SILU)
@@ -829,10 +856,8 @@ void bf16_destroy(Bf16Path* b) {
     cudaFree(b->wstream[i]);
     cudaFree(b->wfc[i]);
     cudaFree(b->bias[i]);
-    cudaFree(b->tfp[i]);
+    cudaFree(b->fc_bias[i]);
   }
-  cudaFree(b->d_bias_off);
-  cudaFree(b->d_bias_w);
   cudaFree(b->fc_a);
   cudaFree(b->partial);
   cudaFree(b->other);
@@ -843,60 +868,113 @@ void bf16_destroy(Bf16Path* b) {
   delete b;
 }
 
-int bf16_pack_weights(Bf16Path* b, const Plan& p, const float* folded, int slot, cudaStream_t st) {
+void bf16_prep_bases(const Bf16Path* b, int slot, PrepBases* bases) {
+  bases->p[PB_WSTREAM] = b->wstream[slot];
+  bases->p[PB_WFC] = b->wfc[slot];
+  bases->p[PB_BIAS] = b->bias[slot];
+  bases->p[PB_FCBIAS] = b->fc_bias[slot];
+}
+
+int bf16_packed_format(const Bf16Path* b, int slot) { return b->packed_fmt[slot]; }
+void bf16_set_packed_format(Bf16Path* b, int slot, int fmt) { b->packed_fmt[slot] = fmt; }
+
+// Phase-1 jobs of the weight-preparation table: every tower / encoder / FC matrix from the folded fp32 set into the
+// core-matrix tiles the kernels stream ([K/8][N][8], in ring order) and the tower biases. For the encoder the LayerNorm
+// weights are folded into the matrices that follow them and every bias becomes a 2-plane slab (see at_bf16_tf.inc); the
+// order below is the order tower_tf_kernel's issuers consume the ring in.
+void bf16_add_prep_jobs(const Bf16Path* b, const Plan& p, PrepList& list) {
   size_t off = 0;
+  auto pack_b = [&](int64_t src, int K, int N, int base, size_t dst_bytes, int64_t row_scale, int period) {
+    PrepJob j{};
+    j.kind = PK_PACK_B; j.phase = 1;
+    j.a[0] = src; j.a[1] = (int64_t)dst_bytes; j.a[2] = row_scale; j.i[0] = K; j.i[1] = N; j.i[2] = base; j.i[3] = period;
+    list.add(j, (int64_t)K * N);
+  };
   for (size_t l = 0; l < b->layer_wt.size(); ++l) {
     const int K = b->layer_k[l], N = b->bias_w[l];
-    pack_b_kernel<<<148, 256, 0, st>>>(folded + b->layer_wt[l], K, N, reinterpret_cast<__nv_bfloat16*>(b->wstream[slot] + off));
-    AT_CUDA_TRY(cudaGetLastError());
+    pack_b(b->layer_wt[l], K, N, PB_WSTREAM, off, -1, 1);
     off += (size_t)K * N * 2;
+    PrepJob g{};
+    g.kind = PK_GATHER_BIAS; g.phase = 1;
+    g.a[0] = b->bias_off[l]; g.a[1] = (int64_t)l * 128; g.i[0] = N;
+    list.add(g, 128);
   }
-  pack_b_kernel<<<148 * 4, 256, 0, st>>>(folded + b->fc_wt, b->fc_flat, b->fc_n, reinterpret_cast<__nv_bfloat16*>(b->wfc[slot]));
-  AT_CUDA_TRY(cudaGetLastError());
-  gather_bias_kernel<<<(unsigned)b->layer_wt.size(), 128, 0, st>>>(folded, b->d_bias_off, b->d_bias_w, (int)b->layer_wt.size(), b->bias[slot]);
-  AT_CUDA_TRY(cudaGetLastError());
-  if (b->tf) {
-    const at_model_desc& d = p.d;
-    __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(b->wstream[slot] + b->conv_stream_bytes);
-    auto pack = [&](const float* wt, const PackSel& sel) -> int {
-      pack_sel_kernel<<<64, 256, 0, st>>>(wt, sel, dst);
-      AT_CUDA_TRY(cudaGetLastError());
-      dst += (size_t)sel.n_rows * sel.k_count;
-      return AT_OK;
-    };
-    auto vec = [&](int dst_off, int64_t src_off, int n, float scale) -> int {
-      copy_scaled_kernel<<<4, 128, 0, st>>>(folded + src_off, b->tfp[slot] + dst_off, n, scale);
-      AT_CUDA_TRY(cudaGetLastError());
-      return AT_OK;
-    };
-    const float qscale = 1.0f / sqrtf((float)kTfDh);
-    const int halves = d.t_ff / 128;
-    for (int l = 0; l < d.t_layers; ++l) {
-      const EncoderLayer& e = p.enc[l];
-      for (int h = 0; h < d.t_heads; ++h) {
-        AT_TRY(pack(folded + e.qkv.wt, PackSel{3 * kTfDh, kTfD, 0, 3 * kTfD, kTfDh, {h * kTfDh, kTfD + h * kTfDh, 2 * kTfD + h * kTfDh}, qscale}));
-        AT_TRY(pack(folded + e.out.wt, PackSel{kTfD, kTfDh, h * kTfDh, kTfD, kTfD, {0, 0, 0}, 1.0f}));
+  if (!b->tf) {
+    pack_b(b->fc_wt, b->fc_flat, b->fc_n, PB_WFC, 0, -1, 1);
+    return;
+  }
+  // trunk FC over the encoder's output: final LayerNorm weight into the matrix rows (row k = token * 128 + channel),
+  // its bias through the matrix into the FC bias
+  pack_b(b->fc_wt, b->fc_flat, b->fc_n, PB_WFC, 0, p.lnf_w, kTfD);
+  {
+    PrepJob j{};
+    j.kind = PK_FC_BIAS; j.phase = 1;
+    j.a[0] = b->fc_bias_off; j.a[1] = b->fc_wt; j.a[2] = p.lnf_b; j.i[0] = b->fc_flat; j.i[1] = b->fc_n; j.i[2] = kTfD;
+    list.add(j, 1);
+  }
+  const at_model_desc& d = p.d;
+  size_t dst = b->conv_stream_bytes;
+  struct Sel { int n_rows, k_count, k0, ld, seg_len, seg_base[3]; float seg0_scale; };
+  auto pack = [&](int64_t src, const Sel& s, int64_t row_scale) {
+    PrepJob j{};
+    j.kind = PK_PACK_SEL; j.phase = 1;
+    j.a[0] = src; j.a[1] = (int64_t)dst; j.a[2] = row_scale;
+    j.i[0] = s.n_rows; j.i[1] = s.k_count; j.i[2] = s.k0; j.i[3] = s.ld; j.i[4] = s.seg_len;
+    j.i[5] = s.seg_base[0]; j.i[6] = s.seg_base[1]; j.i[7] = s.seg_base[2];
+    j.f[0] = s.seg0_scale;
+    list.add(j, (int64_t)s.n_rows * s.k_count);
+    dst += (size_t)s.n_rows * s.k_count * 2;
+  };
+  // bias slab of a GEMM with `n_rows` outputs: bias[col] (+ Wt[:, col] . beta when a LayerNorm precedes the GEMM)
+  auto bias = [&](int64_t bias_src, int64_t wt, int64_t beta, const Sel& s) {
+    PrepJob j{};
+    j.kind = PK_BIAS_SLAB; j.phase = 1;
+    j.a[0] = bias_src; j.a[1] = (int64_t)dst; j.a[2] = wt; j.a[3] = beta;
+    j.i[0] = s.n_rows; j.i[1] = s.k_count; j.i[2] = s.ld; j.i[3] = s.seg_len;
+    j.i[4] = s.seg_base[0]; j.i[5] = s.seg_base[1]; j.i[6] = s.seg_base[2];
+    j.f[0] = s.seg0_scale;
+    list.add(j, (int64_t)2 * s.n_rows * 8);
+    dst += (size_t)2 * s.n_rows * 16;
+  };
+  const float qscale = 1.0f / sqrtf((float)kTfDh);
+  const int halves = d.t_ff / 128;
+  for (int l = 0; l < d.t_layers; ++l) {
+    const EncoderLayer& e = p.enc[l];
+    const Sel out_all{kTfD, kTfD, 0, kTfD, kTfD, {0, 0, 0}, 1.0f};
+    auto out_proj = [&](int h) { pack(e.out.wt, Sel{kTfD, kTfDh, h * kTfDh, kTfD, kTfD, {0, 0, 0}, 1.0f}, -1); };
+    for (int h = 0; h < d.t_heads; ++h) {
+      if (h > 0) {
+        out_proj(h - 1);
+        if (h == 1) bias(e.out.bias, -1, -1, out_all);
       }
-      for (int f = 0; f < halves; ++f) {
-        AT_TRY(pack(folded + e.ff1.wt, PackSel{128, kTfD, 0, d.t_ff, 128, {f * 128, 0, 0}, 1.0f}));
-        AT_TRY(pack(folded + e.ff2.wt, PackSel{kTfD, 128, f * 128, kTfD, kTfD, {0, 0, 0}, 1.0f}));
-      }
-      const TfLayerOffsets& o = b->ttp.tl[l];
-      AT_TRY(vec(o.ln1_w, e.ln1_w, kTfD, 1.0f)); AT_TRY(vec(o.ln1_b, e.ln1_b, kTfD, 1.0f));
-      AT_TRY(vec(o.bq, e.qkv.bias, kTfD, qscale)); AT_TRY(vec(o.bk, e.qkv.bias + kTfD, kTfD, 1.0f));
-      AT_TRY(vec(o.bv, e.qkv.bias + 2 * kTfD, kTfD, 1.0f)); AT_TRY(vec(o.bout, e.out.bias, kTfD, 1.0f));
-      AT_TRY(vec(o.ln2_w, e.ln2_w, kTfD, 1.0f)); AT_TRY(vec(o.ln2_b, e.ln2_b, kTfD, 1.0f));
-      AT_TRY(vec(o.b1, e.ff1.bias, d.t_ff, 1.0f)); AT_TRY(vec(o.b2, e.ff2.bias, kTfD, 1.0f));
+      const Sel qkv{3 * kTfDh, kTfD, 0, 3 * kTfD, kTfDh, {h * kTfDh, kTfD + h * kTfDh, 2 * kTfD + h * kTfDh}, qscale};
+      pack(e.qkv.wt, qkv, e.ln1_w);           // two ring slabs (K halves), contiguous
+      bias(e.qkv.bias, e.qkv.wt, e.ln1_b, qkv);
     }
-    AT_TRY(vec(b->ttp.lnf_w, p.lnf_w, kTfD, 1.0f));
-    AT_TRY(vec(b->ttp.lnf_b, p.lnf_b, kTfD, 1.0f));
+    out_proj(d.t_heads - 1);
+    if (d.t_heads == 1) bias(e.out.bias, -1, -1, out_all);
+    auto linear2 = [&](int f) { pack(e.ff2.wt, Sel{kTfD, 128, f * 128, kTfD, kTfD, {0, 0, 0}, 1.0f}, -1); };
+    for (int f = 0; f < halves; ++f) {
+      if (f > 0) {
+        linear2(f - 1);
+        if (f == 1) bias(e.ff2.bias, -1, -1, out_all);
+      }
+      const Sel l1{128, kTfD, 0, d.t_ff, 128, {f * 128, 0, 0}, 1.0f};
+      pack(e.ff1.wt, l1, e.ln2_w);
+      bias(e.ff1.bias, e.ff1.wt, e.ln2_b, l1);
+    }
+    linear2(halves - 1);
+    if (halves == 1) bias(e.ff2.bias, -1, -1, out_all);
+    // this layer's norm1 belongs to its own q|k|v projection (handled above); the NEXT layer's norm1, or the encoder's
+    // final norm, is applied to this layer's output and folded into whatever consumes it
   }
-  return AT_OK;
 }
 
 int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slot, const void* d_states, int64_t batch, int* n_splits,
                         cudaStream_t st, int64_t* launches, bool with_other) {
   const at_model_desc& d = p.d;
+  const int fmt = b->packed_fmt[slot];
+  if (fmt != FMT_BF16 && fmt != FMT_F16) return fail(AT_E_STATE, "tensor-core path: the weight set holds no packed operands yet");
   if (with_other) {
     // "other" features for the FC's last columns (the grid output of this launch is not used by the tower)
     AT_TRY(launch_features(d.env, 1, d.other_dim, d_states, batch, b->grid, b->other, st));
@@ -924,18 +1002,29 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
   if (b->tf) {
     TowerTfParams t = b->ttp;
     t.conv = tp;
-    t.tfp = b->tfp[slot];
     t.pe = folded + p.pe;
-    if (tp.act0 == AT_ACT_RELU) tower_tf_kernel<AT_ACT_RELU><<<grid, kTfThreads, tower_tf_smem_bytes(), st>>>(t);
-    else tower_tf_kernel<AT_ACT_GELU><<<grid, kTfThreads, tower_tf_smem_bytes(), st>>>(t);
+#define AT_TF_LAUNCH(ACT_)                                                                                          \
+  do {                                                                                                              \
+    if (fmt == FMT_F16) tower_tf_kernel<ACT_, FMT_F16><<<grid, kTfThreads, tower_tf_smem_bytes(), st>>>(t);          \
+    else tower_tf_kernel<ACT_, FMT_BF16><<<grid, kTfThreads, tower_tf_smem_bytes(), st>>>(t);                        \
+  } while (0)
+    if (tp.act0 == AT_ACT_RELU) AT_TF_LAUNCH(AT_ACT_RELU);
+    else AT_TF_LAUNCH(AT_ACT_GELU);
+#undef AT_TF_LAUNCH
   } else {
+#define AT_TOWER_LAUNCH(ACT_)                                                                                       \
+  do {                                                                                                              \
+    if (fmt == FMT_F16) tower_kernel<ACT_, FMT_F16><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp);            \
+    else tower_kernel<ACT_, FMT_BF16><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp);                          \
+  } while (0)
     switch (tp.act0) {
-      case AT_ACT_RELU: tower_kernel<AT_ACT_RELU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
-      case AT_ACT_GELU: tower_kernel<AT_ACT_GELU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
-      case AT_ACT_SILU: tower_kernel<AT_ACT_SILU><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
-      case AT_ACT_TANH: tower_kernel<AT_ACT_TANH><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
-      default: tower_kernel<AT_ACT_SIGMOID><<<grid, kTowerThreads, tower_smem_bytes(), st>>>(tp); break;
+      case AT_ACT_RELU: AT_TOWER_LAUNCH(AT_ACT_RELU); break;
+      case AT_ACT_GELU: AT_TOWER_LAUNCH(AT_ACT_GELU); break;
+      case AT_ACT_SILU: AT_TOWER_LAUNCH(AT_ACT_SILU); break;
+      case AT_ACT_TANH: AT_TOWER_LAUNCH(AT_ACT_TANH); break;
+      default: AT_TOWER_LAUNCH(AT_ACT_SIGMOID); break;
     }
+#undef AT_TOWER_LAUNCH
   }
   AT_CUDA_TRY(cudaGetLastError());
   AT_CUDA_TRY(cudaEventRecord(b->ev[1], st));
@@ -962,7 +1051,7 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
       }
     }
   }
-  FcParams fp{b->fc_a, b->wfc[slot], b->partial, batch, b->n_kc, b->fc_n, per, n_slabs, b->status};
+  FcParams fp{b->fc_a, b->wfc[slot], b->partial, batch, b->n_kc, b->fc_n, per, n_slabs, b->status, fmt};
   AT_CUDA_TRY(cudaEventRecord(b->ev[2], st));
   fc_kernel<<<dim3((unsigned)m_tiles, (unsigned)splits), kFcThreads, fc_smem_bytes(), st>>>(fp);
   AT_CUDA_TRY(cudaGetLastError());
@@ -975,11 +1064,13 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
 }
 
 const float* bf16_partial(const Bf16Path* b) { return b->partial; }
+// trunk FC bias the head kernels must use: with the encoder's final LayerNorm folded in on the transformer path, else null
+const float* bf16_fc_bias(const Bf16Path* b, int slot) { return b->tf ? b->fc_bias[slot] : nullptr; }
 const float* bf16_other(const Bf16Path* b) { return b->other; }
 
 // Unfused tail of the trunk FC: the "other" columns in fp32 as one more partial, then bias + BatchNorm (folded) + activation.
-int bf16_finish_trunk(Bf16Path* b, const Plan& p, const float* folded, int splits, int64_t batch, float* d_trunk, cudaStream_t st,
-                      int64_t* launches) {
+int bf16_finish_trunk(Bf16Path* b, const Plan& p, const float* folded, int slot, int splits, int64_t batch, float* d_trunk,
+                      cudaStream_t st, int64_t* launches) {
   const at_model_desc& d = p.d;
   const Affine& fc = p.shared[0];
   GemmArgs o;
@@ -989,7 +1080,7 @@ int bf16_finish_trunk(Bf16Path* b, const Plan& p, const float* folded, int split
   AT_TRY(launch_gemm(o, 1, st, launches));
   GemmArgs f;
   f.M = batch; f.N = fc.N; f.K = 1;
-  f.partial = b->partial; f.bias = folded + fc.bias; f.act = fc.act;
+  f.partial = b->partial; f.bias = b->tf ? b->fc_bias[slot] : folded + fc.bias; f.act = fc.act;
   f.C = d_trunk; f.ldc = fc.N;
   AT_TRY(launch_splitk_finish(f, splits + 1, st, launches));
   return AT_OK;

@@ -13,8 +13,16 @@ struct Bf16Path;  // opaque: packed bf16 weight sets + scratch of the tcgen05 ke
 // leaves *out null, explains why in *reason and still returns AT_OK.
 int bf16_create(const Plan& plan, int64_t max_batch, Bf16Path** out, std::string* reason);
 void bf16_destroy(Bf16Path* p);
-// folded fp32 set -> bf16 operand images for weight set `slot` (0/1)
-int bf16_pack_weights(Bf16Path* p, const Plan& plan, const float* d_folded, int slot, cudaStream_t stream);
+// folded fp32 set -> 16-bit operand images: the packing steps as jobs of the weight-preparation table (phase 1), and the
+// base pointers of weight set `slot` (0/1) they write to
+class PrepList;
+struct PrepBases;
+void bf16_add_prep_jobs(const Bf16Path* p, const Plan& plan, PrepList& list);
+void bf16_prep_bases(const Bf16Path* p, int slot, PrepBases* bases);
+// operand format (FMT_BF16 / FMT_F16, at_prepjobs.cuh) the 16-bit images of weight set `slot` hold; -1: none yet
+int bf16_packed_format(const Bf16Path* p, int slot);
+void bf16_set_packed_format(Bf16Path* p, int slot, int fmt);
+const float* bf16_fc_bias(const Bf16Path* p, int slot);
 // PackedState[batch] -> split-K partial sums of the first shared FC layer over the tower output, fp32
 // [n_splits][batch][shared[0].N] (bf16_partial), plus -- unless the consumer derives them itself from the packed
 // states (with_other = false) -- the "other" feature vectors (bf16_other)
@@ -23,7 +31,7 @@ int bf16_trunk_partials(Bf16Path* p, const Plan& plan, const float* d_folded, in
 const float* bf16_partial(const Bf16Path* p);
 const float* bf16_other(const Bf16Path* p);
 // partials + other columns + bias, activation -> d_trunk fp32 [batch, shared[0].N] (unfused tail, also the test hook)
-int bf16_finish_trunk(Bf16Path* p, const Plan& plan, const float* d_folded, int n_splits, int64_t batch, float* d_trunk,
+int bf16_finish_trunk(Bf16Path* p, const Plan& plan, const float* d_folded, int slot, int n_splits, int64_t batch, float* d_trunk,
                       cudaStream_t stream, int64_t* launches);
 // Same as bf16_trunk_partials with every intermediate buffer inside the library's static device array
 // (no allocation, batch <= bf16_static_max_batch()); *partial / *other point into that array.

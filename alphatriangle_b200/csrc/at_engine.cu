@@ -8,6 +8,7 @@
 #include "at_engine.cuh"
 #include "at_fp32.cuh"
 #include "at_heads.cuh"
+#include "at_prepjobs.cuh"
 
 namespace at {
 
@@ -70,6 +71,8 @@ struct at_engine {
   Bf16Path* bf16 = nullptr;  // tcgen05 path state (null if the configuration is not covered)
   std::string bf16_reason;
   uint2* heads_frag[2] = {nullptr, nullptr};  // per weight set: head matrices as bf16 MMA fragments (null: shape not covered)
+  PrepTable prep;  // every fold / pack step of a weight load, run as two launches
+  int tc_fmt = FMT_BF16;  // operand format weight loads pack for: the one the last tensor-core evaluation asked for
 
   int64_t last_launches = 0;
 };
@@ -274,13 +277,41 @@ int end_eval(at_engine* e, cudaStream_t st) {
   return AT_OK;
 }
 
+bool is_tc(int precision) { return precision == AT_PREC_BF16 || precision == AT_PREC_F16; }
+int tc_format(int precision) { return precision == AT_PREC_F16 ? FMT_F16 : FMT_BF16; }
+
 int check_precision(at_engine* e, int precision) {
   if (precision == AT_PREC_FP32) return AT_OK;
-  if (precision == AT_PREC_BF16) {
+  if (is_tc(precision)) {
     if (e->bf16) return AT_OK;
-    return fail(AT_E_UNSUPPORTED, "bf16 path unavailable for this configuration: " + e->bf16_reason);
+    return fail(AT_E_UNSUPPORTED, "tensor-core path unavailable for this configuration: " + e->bf16_reason);
   }
   return fail(AT_E_INVALID, "unknown precision");
+}
+
+PrepBases prep_bases(at_engine* e, const float* d_image, int set);
+
+// The 16-bit operand images of the active weight set are kept in ONE format. An evaluation that wants the other one
+// re-packs them from the folded fp32 set on its own stream (two formats are not meant to alternate call by call: an
+// engine normally serves one precision). Later weight loads pack for the format asked for last.
+int ensure_format(at_engine* e, int fmt, cudaStream_t st) {
+  e->tc_fmt = fmt;
+  if (bf16_packed_format(e->bf16, e->active) == fmt) return AT_OK;
+  AT_CUDA_TRY(cudaStreamWaitEvent(st, e->last_use[e->active], 0));  // evaluations still reading the old images
+  const PrepBases bases = prep_bases(e, nullptr, e->active);
+  AT_TRY(prep_run(e->prep, bases, fmt, st, nullptr, /*first_phase=*/1));
+  bf16_set_packed_format(e->bf16, e->active, fmt);
+  AT_CUDA_TRY(cudaEventRecord(e->ready[e->active], st));
+  return AT_OK;
+}
+
+PrepBases prep_bases(at_engine* e, const float* d_image, int set) {
+  PrepBases bases{};
+  bases.p[PB_IMAGE] = const_cast<float*>(d_image);
+  bases.p[PB_FOLDED] = e->folded[set];
+  if (e->bf16) bf16_prep_bases(e->bf16, set, &bases);
+  bases.p[PB_FRAGS] = e->heads_frag[set];
+  return bases;
 }
 
 }  // namespace
@@ -326,6 +357,10 @@ static HeadsParams heads_params(const at_engine* e, const float* W, int slot) {
   hp.pol_hidden = p.policy[0].N; hp.val_hidden = p.value[0].N; hp.actions = p.action_dim; hp.atoms = p.d.num_atoms;
   hp.v_min = p.d.v_min; hp.v_max = p.d.v_max;
   hp.frags = e->heads_frag[slot];
+  if (e->bf16 && W) {
+    hp.fmt = bf16_packed_format(e->bf16, slot);
+    if (const float* fb = bf16_fc_bias(e->bf16, slot)) hp.trunk_bias = fb;  // encoder's final LayerNorm folded in
+  }
   return hp;
 }
 
@@ -418,6 +453,17 @@ int at_engine_create(const at_model_desc* desc, int device, int64_t max_batch, a
       if (rc != AT_OK) { at_engine_destroy(e); return rc; }
     }
   }
+  {
+    PrepList jobs;
+    fold_add_prep_jobs(p, jobs);
+    if (e->bf16) bf16_add_prep_jobs(e->bf16, p, jobs);
+    if (e->heads_frag[0]) {
+      const int64_t src[4] = {p.policy[0].wt, p.value[0].wt, p.policy[1].wt, p.value[1].wt};
+      heads_add_prep_jobs(heads_params(e, nullptr, 0), src, jobs);
+    }
+    rc = prep_upload(jobs, &e->prep);
+    if (rc != AT_OK) { at_engine_destroy(e); return rc; }
+  }
   AT_CUDA_TRY(cudaDeviceSynchronize());
   *out = e;
   return AT_OK;
@@ -428,6 +474,7 @@ int at_engine_destroy(at_engine* e) {
   DeviceGuard guard(e->device);
   cudaDeviceSynchronize();
   bf16_destroy(e->bf16);
+  prep_free(&e->prep);
   for (int i = 0; i < 2; ++i) {
     cudaFree(e->folded[i]);
     cudaFree(e->heads_frag[i]);
@@ -480,12 +527,8 @@ static int fill_weight_set(at_engine* e, const float* d_image, int64_t n_floats,
   // evaluations that still read the set about to be overwritten must drain first; so must an earlier publication into it
   AT_CUDA_TRY(cudaStreamWaitEvent(st, e->last_use[target], 0));
   if (e->pending == target) AT_CUDA_TRY(cudaStreamWaitEvent(st, e->ready[target], 0));
-  AT_TRY(fold_weights(e->plan, d_image, e->folded[target], st));
-  if (e->bf16) AT_TRY(bf16_pack_weights(e->bf16, e->plan, e->folded[target], target, st));
-  if (e->heads_frag[target]) {
-    const HeadsParams hp = heads_params(e, e->folded[target], target);
-    AT_TRY(heads_pack_frags(hp, e->heads_frag[target], st));
-  }
+  AT_TRY(prep_run(e->prep, prep_bases(e, d_image, target), e->tc_fmt, st, nullptr));
+  if (e->bf16) bf16_set_packed_format(e->bf16, target, e->tc_fmt);
   AT_CUDA_TRY(cudaEventRecord(e->ready[target], st));
   e->version[target] = version;
   if (deferred && e->active >= 0) {
@@ -510,7 +553,7 @@ int64_t at_engine_weight_version(const at_engine* e) { return (e && e->active >=
 int at_engine_supports(const at_engine* e, int precision) {
   if (!e) return 0;
   if (precision == AT_PREC_FP32) return 1;
-  if (precision == AT_PREC_BF16) {
+  if (is_tc(precision)) {
     if (e->bf16) return 1;
     set_error(e->bf16_reason);
     return 0;
@@ -536,9 +579,10 @@ int at_engine_bf16_trunk(at_engine* e, const void* d_states, int64_t batch, floa
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const float* W = nullptr;
   AT_TRY(begin_eval(e, st, &W));
+  AT_TRY(ensure_format(e, e->tc_fmt, st));
   int splits = 0;
   AT_TRY(bf16_trunk_partials(e->bf16, e->plan, W, e->active, d_states, batch, &splits, st, &e->last_launches));
-  AT_TRY(bf16_finish_trunk(e->bf16, e->plan, W, splits, batch, d_trunk, st, &e->last_launches));
+  AT_TRY(bf16_finish_trunk(e->bf16, e->plan, W, e->active, splits, batch, d_trunk, st, &e->last_launches));
   return end_eval(e, st);
 }
 
@@ -562,6 +606,7 @@ int at_engine_evaluate_packed_static(at_engine* e, const void* d_states, int64_t
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const float* W = nullptr;
   AT_TRY(begin_eval(e, st, &W));
+  AT_TRY(ensure_format(e, e->tc_fmt, st));
   int splits = 0;
   const float *partial = nullptr, *other = nullptr;
   int rc = bf16_trunk_partials_static(e->bf16, p, W, e->active, d_states, batch, &splits, &partial, &other, st, &e->last_launches);
@@ -608,14 +653,15 @@ int at_engine_evaluate_packed(at_engine* e, int precision, const void* d_states,
   if (!d_states || !d_policy || !d_value || !d_flags) return fail(AT_E_INVALID, "at_engine_evaluate_packed: null pointer");
   if ((reinterpret_cast<uintptr_t>(d_states) & 15u) != 0) return fail(AT_E_INVALID, "at_engine_evaluate_packed: d_states must be 16-byte aligned");
   AT_TRY(check_precision(e, precision));
-  if (precision == AT_PREC_BF16 && batch > e->max_batch)
+  if (is_tc(precision) && batch > e->max_batch)
     return fail(AT_E_INVALID, "at_engine_evaluate_packed: batch exceeds the engine's max_batch");
   DeviceGuard guard(e->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const float* W = nullptr;
   AT_TRY(begin_eval(e, st, &W));
   const Plan& p = e->plan;
-  if (precision == AT_PREC_BF16) {
+  if (is_tc(precision)) {
+    AT_TRY(ensure_format(e, tc_format(precision), st));
     int splits = 0;
     // the tensor-core head kernel derives the other-feature vectors itself: no separate feature launch on this path
     const bool heads_own_other = heads_shape_fused(p) && heads_take_states(e, heads_params(e, W, e->active));
@@ -634,7 +680,7 @@ int at_engine_evaluate_packed(at_engine* e, int precision, const void* d_states,
       }
     }
     float* trunk1 = p.shared.size() == 1 ? e->trunk : e->mlp_b;
-    AT_TRY(bf16_finish_trunk(e->bf16, p, W, splits, batch, trunk1, st, &e->last_launches));
+    AT_TRY(bf16_finish_trunk(e->bf16, p, W, e->active, splits, batch, trunk1, st, &e->last_launches));
     AT_TRY(run_heads(e, W, trunk1, p.shared[0].N, false, 1, batch, d_policy, d_value, d_flags, st));
     AT_TRY(launch_merge_status(bf16_status_ptr(e->bf16), d_flags, st, &e->last_launches));
     return end_eval(e, st);

@@ -74,7 +74,8 @@ struct Plan {
 
 int build_plan(const at_model_desc& d, Plan& plan);  // at_plan.cu
 
-// at_prep.cu: image -> folded fp32 weight set
-int fold_weights(const Plan& plan, const float* d_image, float* d_folded, cudaStream_t stream);
+// at_prep.cu: the image -> folded fp32 weight set steps, appended to a weight-preparation job table (at_prepjobs.cuh)
+class PrepList;
+void fold_add_prep_jobs(const Plan& plan, PrepList& list);
 
 }  // namespace at

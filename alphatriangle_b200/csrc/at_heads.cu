@@ -15,6 +15,7 @@
 #include "at_features.cuh"
 #include "at_fp32.cuh"
 #include "at_heads.cuh"
+#include "at_prepjobs.cuh"
 
 namespace at {
 
@@ -244,15 +245,25 @@ __global__ void __launch_bounds__(kThreads, 2) heads_fused_kernel(const HeadsPar
 
 constexpr int kPadH = 8;  // bf16 padding of an activation row: pitch (K+8)*2 bytes keeps fragment loads / stores conflict-free
 
-__device__ __forceinline__ void mma_bf16_16816(float (&d)[4], const uint32_t (&a)[4], const uint2 b) {
-  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-               : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
+// FMT: operand format of activations and packed weights (FMT_BF16 / FMT_F16, at_prepjobs.cuh), fp32 accumulate either way
+template <int FMT>
+__device__ __forceinline__ void mma_16816(float (&d)[4], const uint32_t (&a)[4], const uint2 b) {
+  if constexpr (FMT == FMT_F16)
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
+  else
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b.x), "r"(b.y));
 }
 
-__device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
-  const __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
-  return *reinterpret_cast<const uint32_t*>(&v);
+template <int FMT>
+__device__ __forceinline__ uint32_t pack16x2(float lo, float hi) {
+  uint32_t w;
+  if constexpr (FMT == FMT_F16) asm("cvt.rn.satfinite.f16x2.f32 %0, %1, %2;" : "=r"(w) : "f"(hi), "f"(lo));
+  else asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w) : "f"(hi), "f"(lo));
+  return w;
 }
 
 // A fragments of a [32][K] bf16 tile (row pitch K + kPadH) for both 16-row halves: a[m][kt][0..3].
@@ -273,7 +284,7 @@ __device__ __forceinline__ void load_a_frags(const __nv_bfloat16* A_s, int pitch
 }
 
 // Tiles first, first + step, ... < n_tiles of one packed matrix: acc[m] = A[m] x B(tile); `done(tile, acc)` stores them.
-template <int KT, typename Done>
+template <int KT, int FMT, typename Done>
 __device__ __forceinline__ void mma_tiles(const uint32_t (&a)[2][KT][4], const uint2* __restrict__ frags, int first, int step,
                                           int n_tiles, Done&& done) {
   const int lane = threadIdx.x % 32;
@@ -292,8 +303,8 @@ __device__ __forceinline__ void mma_tiles(const uint32_t (&a)[2][KT][4], const u
     float acc[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
 #pragma unroll
     for (int kt = 0; kt < KT; ++kt) {
-      mma_bf16_16816(acc[0], a[0][kt], b[kt]);
-      mma_bf16_16816(acc[1], a[1][kt], b[kt]);
+      mma_16816<FMT>(acc[0], a[0][kt], b[kt]);
+      mma_16816<FMT>(acc[1], a[1][kt], b[kt]);
     }
     done(tile, acc);
 #pragma unroll
@@ -318,19 +329,6 @@ __host__ __device__ inline FragLayout frag_layout(const HeadsParams& p) {
   L.v2 = L.p2 + (size_t)L.p2_tiles * (p.pol_hidden / 16) * 32;
   L.total = L.v2 + (size_t)L.v2_tiles * (p.val_hidden / 16) * 32;
   return L;
-}
-
-// Wt [K][N] fp32 -> [N tiles][K/16][32 lanes] uint2: lane 4g+t of tile j, k-block i holds W[16i+2t, +1][8j+g] and
-// W[16i+2t+8, +9][8j+g] (the m16n8k16 "col" B fragment); columns >= N are zero.
-__global__ void pack_frag_kernel(const float* __restrict__ Wt, int K, int N, int n_tiles, uint2* __restrict__ out) {
-  const int KT = K / 16;
-  const int total = n_tiles * KT * 32;
-  for (int idx = blockIdx.x * blockDim.x + threadIdx.x; idx < total; idx += gridDim.x * blockDim.x) {
-    const int lane = idx % 32, kt = (idx / 32) % KT, j = idx / (32 * KT);
-    const int g = lane >> 2, t = lane & 3, n = 8 * j + g, k0 = 16 * kt + 2 * t;
-    auto w = [&](int k) { return n < N ? Wt[(size_t)k * N + n] : 0.0f; };
-    out[idx] = make_uint2(pack_bf16x2(w(k0), w(k0 + 1)), pack_bf16x2(w(k0 + 8), w(k0 + 9)));
-  }
 }
 
 
@@ -414,7 +412,7 @@ __device__ __forceinline__ uint32_t softmax_epilogue_regs(const HeadsParams& p, 
 constexpr int kMmaWarps = 16;  // one block per SM at 128 registers: twice the warps of the CUDA-core kernel to hide L2 latency
 constexpr int kMmaThreads = kMmaWarps * 32;
 
-template <int KT>
+template <int KT, int FMT>
 __global__ void __launch_bounds__(kMmaThreads, 1) heads_mma_kernel(const HeadsParams p) {
   constexpr int K = KT * 16, PITCH = K + kPadH;
   extern __shared__ __align__(16) float sm[];
@@ -478,7 +476,7 @@ __global__ void __launch_bounds__(kMmaThreads, 1) heads_mma_kernel(const HeadsPa
         }
         v.x = act_small(v.x, p.act); v.y = act_small(v.y, p.act); v.z = act_small(v.z, p.act); v.w = act_small(v.w, p.act);
       }
-      *reinterpret_cast<uint2*>(t_s + b * PITCH + n) = make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+      *reinterpret_cast<uint2*>(t_s + b * PITCH + n) = make_uint2(pack16x2<FMT>(v.x, v.y), pack16x2<FMT>(v.z, v.w));
     }
   }
   __syncthreads();
@@ -493,13 +491,13 @@ __global__ void __launch_bounds__(kMmaThreads, 1) heads_mma_kernel(const HeadsPa
 #pragma unroll
       for (int m = 0; m < 2; ++m) {
         __nv_bfloat16* r0 = H_s + (m * 16 + g) * PITCH + n;
-        *reinterpret_cast<uint32_t*>(r0) = pack_bf16x2(act_small(acc[m][0] + b0v, p.act), act_small(acc[m][1] + b1v, p.act));
-        *reinterpret_cast<uint32_t*>(r0 + 8 * PITCH) = pack_bf16x2(act_small(acc[m][2] + b0v, p.act), act_small(acc[m][3] + b1v, p.act));
+        *reinterpret_cast<uint32_t*>(r0) = pack16x2<FMT>(act_small(acc[m][0] + b0v, p.act), act_small(acc[m][1] + b1v, p.act));
+        *reinterpret_cast<uint32_t*>(r0 + 8 * PITCH) = pack16x2<FMT>(act_small(acc[m][2] + b0v, p.act), act_small(acc[m][3] + b1v, p.act));
       }
     };
   };
-  mma_tiles<KT>(a, p.frags + L.p1, warp, kMmaWarps, L.p1_tiles, hidden_done(hp_s, p.bp1));
-  mma_tiles<KT>(a, p.frags + L.v1, warp, kMmaWarps, L.v1_tiles, hidden_done(hv_s, p.bv1));
+  mma_tiles<KT, FMT>(a, p.frags + L.p1, warp, kMmaWarps, L.p1_tiles, hidden_done(hp_s, p.bp1));
+  mma_tiles<KT, FMT>(a, p.frags + L.v1, warp, kMmaWarps, L.v1_tiles, hidden_done(hv_s, p.bv1));
   __syncthreads();
 
   // ---- logits (fp32, + bias) into shared memory ----
@@ -516,11 +514,11 @@ __global__ void __launch_bounds__(kMmaThreads, 1) heads_mma_kernel(const HeadsPa
     };
   };
   load_a_frags<KT>(hp_s, PITCH, a);
-  mma_tiles<KT>(a, p.frags + L.p2, warp, kMmaWarps, L.p2_tiles, logits_done(pl_s, AP, p.bp2, p.actions));
+  mma_tiles<KT, FMT>(a, p.frags + L.p2, warp, kMmaWarps, L.p2_tiles, logits_done(pl_s, AP, p.bp2, p.actions));
   // value tiles go to the warps from the top down: those have the fewest policy tiles
   if (kMmaWarps - 1 - warp < L.v2_tiles) {
     load_a_frags<KT>(hv_s, PITCH, a);
-    mma_tiles<KT>(a, p.frags + L.v2, kMmaWarps - 1 - warp, kMmaWarps, L.v2_tiles, logits_done(vl_s, VP, p.bv2, p.atoms));
+    mma_tiles<KT, FMT>(a, p.frags + L.v2, kMmaWarps - 1 - warp, kMmaWarps, L.v2_tiles, logits_done(vl_s, VP, p.bv2, p.atoms));
   }
   __syncthreads();
 
@@ -575,18 +573,20 @@ bool heads_mma_supported(const HeadsParams& p) {
 
 size_t heads_frag_count(const HeadsParams& p) { return frag_layout(p).total; }
 
-int heads_pack_frags(const HeadsParams& p, uint2* dst, cudaStream_t stream) {
+// Phase-1 jobs of the weight-preparation table: the four head matrices (folded fp32 Wt at float offsets src[0..3] =
+// policy hidden, value hidden, policy logits, value logits) into mma.sync B-fragment order.
+void heads_add_prep_jobs(const HeadsParams& p, const int64_t src[4], PrepList& list) {
   const FragLayout L = frag_layout(p);
-  auto pack = [&](const float* wt, int K, int N, int tiles, size_t off) -> int {
-    pack_frag_kernel<<<64, 256, 0, stream>>>(wt, K, N, tiles, dst + off);
-    AT_CUDA_TRY(cudaGetLastError());
-    return AT_OK;
+  auto pack = [&](int64_t from, int K, int N, int tiles, size_t off) {
+    PrepJob j{};
+    j.kind = PK_PACK_FRAG; j.phase = 1;
+    j.a[0] = from; j.a[1] = (int64_t)off; j.i[0] = K; j.i[1] = N; j.i[2] = tiles;
+    list.add(j, (int64_t)tiles * (K / 16) * 32 * 4);
   };
-  AT_TRY(pack(p.wp1, p.trunk_n, p.pol_hidden, L.p1_tiles, L.p1));
-  AT_TRY(pack(p.wv1, p.trunk_n, p.val_hidden, L.v1_tiles, L.v1));
-  AT_TRY(pack(p.wp2, p.pol_hidden, p.actions, L.p2_tiles, L.p2));
-  AT_TRY(pack(p.wv2, p.val_hidden, p.atoms, L.v2_tiles, L.v2));
-  return AT_OK;
+  pack(src[0], p.trunk_n, p.pol_hidden, L.p1_tiles, L.p1);
+  pack(src[1], p.trunk_n, p.val_hidden, L.v1_tiles, L.v1);
+  pack(src[2], p.pol_hidden, p.actions, L.p2_tiles, L.p2);
+  pack(src[3], p.val_hidden, p.atoms, L.v2_tiles, L.v2);
 }
 
 int launch_heads_mma(const HeadsParams& p, cudaStream_t stream, int64_t* launches) {
@@ -598,13 +598,19 @@ int launch_heads_mma(const HeadsParams& p, cudaStream_t stream, int64_t* launche
   const size_t smem = heads_mma_smem(p);
   const unsigned grid = (unsigned)((p.batch + TB - 1) / TB);
   // the opt-in is per device and cheap; set on every launch so several engines on different GPUs stay correct
+#define AT_HEADS_LAUNCH(KT_, FMT_)                                                                                              \
+  do {                                                                                                                          \
+    AT_CUDA_TRY(cudaFuncSetAttribute(heads_mma_kernel<KT_, FMT_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));    \
+    heads_mma_kernel<KT_, FMT_><<<grid, kMmaThreads, smem, stream>>>(p);                                                        \
+  } while (0)
   if (mma_kt(p) == 8) {
-    AT_CUDA_TRY(cudaFuncSetAttribute(heads_mma_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    heads_mma_kernel<8><<<grid, kMmaThreads, smem, stream>>>(p);
+    if (p.fmt == FMT_F16) AT_HEADS_LAUNCH(8, FMT_F16);
+    else AT_HEADS_LAUNCH(8, FMT_BF16);
   } else {
-    AT_CUDA_TRY(cudaFuncSetAttribute(heads_mma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    heads_mma_kernel<4><<<grid, kMmaThreads, smem, stream>>>(p);
+    if (p.fmt == FMT_F16) AT_HEADS_LAUNCH(4, FMT_F16);
+    else AT_HEADS_LAUNCH(4, FMT_BF16);
   }
+#undef AT_HEADS_LAUNCH
   AT_CUDA_TRY(cudaGetLastError());
   if (launches) ++*launches;
   return AT_OK;

@@ -26,7 +26,8 @@ struct HeadsParams {
   uint32_t* flags;
   int w_stage_off;         // filled by the launcher: float offset of the weight staging area in shared memory
   const uint32_t* status;  // optional: tcgen05 pipeline status word folded into the flags
-  const uint2* frags;      // tensor-core variant: the four head matrices as bf16 mma.sync B fragments (heads_pack_frags), else null
+  int fmt;                 // operand format of `frags` and of the activations fed to the MMAs (FMT_BF16 / FMT_F16)
+  const uint2* frags;      // tensor-core variant: the four head matrices as bf16 mma.sync B fragments (heads_add_prep_jobs), else null
   // tensor-core variant, optional: derive the other-feature vectors from the packed states in the prologue instead of
   // reading `other` (same arithmetic as the feature kernel, at_features.cuh); needs env_cols <= 32
   const PackedState* states;
@@ -41,7 +42,9 @@ int launch_heads_fused(const HeadsParams& p, cudaStream_t stream, int64_t* launc
 // weights pre-packed into B-fragment order (one coalesced 256-byte load per 16x8 tile, no shared-memory staging).
 bool heads_mma_supported(const HeadsParams& p);
 size_t heads_frag_count(const HeadsParams& p);  // uint2 elements of the packed image
-int heads_pack_frags(const HeadsParams& p, uint2* dst, cudaStream_t stream);  // from p.wp1 / wv1 / wp2 / wv2
+class PrepList;
+// the fragment packing as jobs of the weight-preparation table; src[] = folded-set float offsets of wp1 / wv1 / wp2 / wv2
+void heads_add_prep_jobs(const HeadsParams& p, const int64_t src[4], PrepList& list);
 int launch_heads_mma(const HeadsParams& p, cudaStream_t stream, int64_t* launches);
 
 }  // namespace at

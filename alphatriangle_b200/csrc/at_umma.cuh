@@ -32,6 +32,20 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
+// try_wait with a suspend-time hint: the hardware may park the thread until the phase completes or `hint_ns` has passed,
+// whichever comes first, instead of returning after its short default time limit (measured here: ~60 cycles), so a waiting
+// warp stops competing for issue slots with the warps that are doing the work it waits for.
+__device__ __forceinline__ bool mbar_try_wait_hint(uint32_t bar, uint32_t parity, uint32_t hint_ns) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity), "r"(hint_ns)
+      : "memory");
+  return ok != 0;
+}
 // Non-suspending probe: returns at once either way (try_wait may park the thread for a hardware-chosen time first).
 __device__ __forceinline__ bool mbar_test_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
@@ -100,14 +114,16 @@ __device__ __forceinline__ uint64_t smem_desc(uint32_t addr, uint32_t lbo_bytes,
   return d;
 }
 
-// Instruction descriptor, kind::f16: bf16 x bf16 -> fp32, A and B K-major, M x N tile.
-__host__ __device__ constexpr uint32_t idesc_bf16(uint32_t m, uint32_t n) {
+// Instruction descriptor, kind::f16: 16-bit x 16-bit -> fp32, A and B K-major, M x N tile. `bf16` selects the operand
+// format of both A and B: 1 = bf16 (8-bit mantissa, fp32's exponent range), 0 = fp16 (11-bit mantissa, max 65504).
+__host__ __device__ constexpr uint32_t idesc_16(uint32_t m, uint32_t n, uint32_t bf16) {
   return (1u << 4)            // D format: f32
-         | (1u << 7)          // A format: bf16
-         | (1u << 10)         // B format: bf16
+         | (bf16 << 7)        // A format
+         | (bf16 << 10)       // B format
          | ((n >> 3) << 17)   // N / 8
          | ((m >> 4) << 24);  // M / 16
 }
+__host__ __device__ constexpr uint32_t idesc_bf16(uint32_t m, uint32_t n) { return idesc_16(m, n, 1u); }
 
 // D[tmem] (+)= A[smem] * B[smem]^T ; issued by ONE thread on behalf of the CTA
 __device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, bool accumulate) {

@@ -33,15 +33,20 @@ class NetworkEvaluationError(Exception):
     """Raised for every failure of evaluate_state / evaluate_batch (network.py:26-29)."""
 
 
-_PRECISIONS = {"fp32": _lib.PREC_FP32, "bf16": _lib.PREC_BF16}
+_PRECISIONS = {"fp32": _lib.PREC_FP32, "bf16": _lib.PREC_BF16, "f16": _lib.PREC_F16}
 
 
 class NeuralNetwork:
     """Conforms to trimcts.AlphaZeroNetworkInterface, evaluating on one B200.
 
     Extra keyword arguments (not in the reference): `precision` -- "fp32" (parity
-    path, max-abs 1e-4 against the reference), "bf16" (tcgen05 path, policy
-    KL <= 1e-3) or "auto" (bf16 when the configuration is covered, else fp32);
+    path, max-abs 1e-4 against the reference), "f16" / "bf16" (the tcgen05 path with
+    fp16 or bf16 operands, fp32 accumulation: policy KL <= 1e-3; fp16's 11-bit mantissa
+    holds that bound also for near-deterministic policies, bf16's 8 bits hold it up to
+    policies of about two nats) or "auto": fp16 when the
+    tcgen05 path covers the configuration and the network has normalisation layers
+    (activations then stay far inside fp16's range; conversions saturate at 65504),
+    bf16 when it has none, fp32 when the tcgen05 path does not cover the configuration.
     `max_batch` -- capacity of the engine's staging buffers (larger batches are
     evaluated in slices).
     """
@@ -78,13 +83,16 @@ class NeuralNetwork:
 
         self.engine = Engine(model_config, env_config, device, max_batch)
         if precision == "auto":
-            self.precision = _lib.PREC_BF16 if self.engine.supports(_lib.PREC_BF16) else _lib.PREC_FP32
+            if not self.engine.supports(_lib.PREC_BF16):
+                self.precision = _lib.PREC_FP32
+            else:
+                self.precision = _lib.PREC_F16 if model_config.USE_BATCH_NORM else _lib.PREC_BF16
         elif precision in _PRECISIONS:
             self.precision = _PRECISIONS[precision]
             if not self.engine.supports(self.precision):
                 raise _lib.LibraryError(f"precision {precision!r} unavailable: {_lib.last_error()}")
         else:
-            raise ValueError(f"precision must be 'auto', 'fp32' or 'bf16', got {precision!r}")
+            raise ValueError(f"precision must be 'auto', 'fp32', 'bf16' or 'f16', got {precision!r}")
         self._action_keys = tuple(range(self.action_dim))
         # parameters and float buffers become views into one flat buffer in the engine's image order (flat.py): in-place
         # updates (optimiser steps, load_state_dict, an NCCL receive) write the engine's input directly
@@ -264,7 +272,7 @@ class NeuralNetwork:
     def evaluate_packed(self, packed: torch.Tensor):
         """PackedState tensor uint8 [B,80] on the device -> (probs [B,A], value [B]) on the device, no host sync."""
         self._sync_engine()
-        if packed.shape[0] > self.engine.max_batch and self.precision == _lib.PREC_BF16:
+        if packed.shape[0] > self.engine.max_batch and self.precision in _lib.TENSOR_CORE_PRECISIONS:
             raise ValueError(f"batch {packed.shape[0]} exceeds max_batch {self.engine.max_batch}")
         probs, value, _flags = self.engine.evaluate_packed(packed, self.precision)
         return probs, value

@@ -299,7 +299,7 @@ class Workload:
         self.torch, self._lib = torch, _lib
         env, mc = at.EnvConfig(), model_config(name)
         self.nn = at.NeuralNetwork(mc, env, at.TrainConfig(), dev, precision=precision, max_batch=batch)
-        self.prec_name = "bf16" if self.nn.precision == _lib.PREC_BF16 else "fp32"
+        self.prec_name = _lib.PRECISION_NAMES[self.nn.precision]
         # weights: rank 0 owns them (the trainer's role); every other rank receives the image over NCCL
         if rank == 0 or not weights_from_rank0:
             self.nn.set_weights(synth_state_dict(self.nn.get_weights(), 1))
@@ -356,7 +356,7 @@ class Workload:
     def kernel_times(self, steps, flush):
         """Second pass, same conditions: the engine's own event pair around the dominant kernel, read after every step."""
         tower, fc = [], []
-        if self.nn.precision != self._lib.PREC_BF16:
+        if self.nn.precision not in self._lib.TENSOR_CORE_PRECISIONS:
             return None
         for i in range(steps):
             flush.fill_(i & 0xFF)
@@ -520,6 +520,7 @@ def measure_publication(w, steps, flush):
                 p1.record(pub.stream)
                 pubs.append((p0, p1))
             w.step()
+            torch.cuda.current_stream(w.dev).synchronize()  # the host consumes each batch (never waits for the side stream)
         end.record()
         pub.wait()
         w.barrier()
@@ -644,7 +645,7 @@ def main():
     ap.add_argument("--impl", choices=["ours", "reference"], default="ours")
     ap.add_argument("--workload", choices=list(WORKLOADS), default="conv_only")
     ap.add_argument("--batch", type=int, default=4096, help="states per GPU per step")
-    ap.add_argument("--precision", choices=["auto", "fp32", "bf16"], default="auto")
+    ap.add_argument("--precision", choices=["auto", "fp32", "bf16", "f16"], default="auto")
     ap.add_argument("--ref-sample", type=int, default=0, help="states per CPU-reference step (0 = --batch, like for like)")
     ap.add_argument("--cpu-budget", type=float, default=18.0, help="seconds of CPU baseline work in the default run")
     ap.add_argument("--sustained", type=float, default=2.5, help="seconds of back-to-back steps for the sustained record (0 = skip)")

@@ -50,7 +50,10 @@ enum at_activation { AT_ACT_NONE = 0, AT_ACT_RELU = 1, AT_ACT_GELU = 2, AT_ACT_S
 /* precision of the forward pass */
 enum at_precision {
   AT_PREC_FP32 = 0, /* fp32 CUDA-core path, any configuration; parity max-abs 1e-4 */
-  AT_PREC_BF16 = 1  /* tcgen05/TMEM bf16 path, fp32 accumulate; parity policy KL <= 1e-3 */
+  AT_PREC_BF16 = 1, /* tcgen05/TMEM path, bf16 operands (8-bit mantissa, fp32's range), fp32 accumulate */
+  AT_PREC_F16 = 2   /* the same kernels with fp16 operands (11-bit mantissa; conversions saturate at +-65504): 8x smaller
+                     * rounding error on every operand, the format to use for trained networks whose activations stay
+                     * in fp16's range (any network with normalisation layers); parity policy KL <= 1e-3 */
 };
 
 /* Game geometry: trianglengin.EnvConfig as read at extractor.py:25,39,50. */

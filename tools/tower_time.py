@@ -16,14 +16,15 @@ from alphatriangle_b200.synth import synth_state_dict, synth_states  # noqa: E40
 B = int(sys.argv[1]) if len(sys.argv) > 1 else 4096
 reps = int(sys.argv[2]) if len(sys.argv) > 2 else 5
 env, mc = at.EnvConfig(), at.ModelConfig(USE_TRANSFORMER=False)
-nn = at.NeuralNetwork(mc, env, None, torch.device("cuda:0"), precision="bf16", max_batch=B)
+nn = at.NeuralNetwork(mc, env, None, torch.device("cuda:0"), precision=os.environ.get("AT_PREC", "bf16"), max_batch=B)
 nn.set_weights(synth_state_dict(nn.get_weights(), 1))
 base = pack_states(synth_states(256, env, seed=5), env)
 packed = torch.from_numpy(np.tile(base, (-(-B // 256), 1))[:B]).cuda()
 ts = []
 for _ in range(reps):
-    nn.engine.evaluate_packed(packed, _lib.PREC_BF16)
+    probs, value, _flags = nn.engine.evaluate_packed(packed, nn.precision)
     ts.append(nn.engine.kernel_times())
+chk = f"{float(value.double().sum()):.9f}/{float((probs.double() * torch.arange(probs.shape[1], device=probs.device)).sum()):.6f}"
 t = ts[-1]
-print(f"debug={os.environ.get('AT_TOWER_DEBUG', '0')} B={B} tower_ms={min(x['tower_ms'] for x in ts):.4f} fc_ms={t['fc_ms']:.4f} "
-      f"states/s(tower)={B / (min(x['tower_ms'] for x in ts) * 1e-3):.0f}")
+print(f"{_lib.PRECISION_NAMES[nn.precision]} debug={os.environ.get('AT_TOWER_DEBUG', '0')} B={B} tower_ms={min(x['tower_ms'] for x in ts):.4f} fc_ms={t['fc_ms']:.4f} "
+      f"states/s(tower)={B / (min(x['tower_ms'] for x in ts) * 1e-3):.0f} chk={chk}")
