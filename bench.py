@@ -531,6 +531,7 @@ def measure_publication(w, steps, flush):
     w.check_flags("the publication run")
     vals = reduce_max(torch, w.dev, w.world, [base_ms, with_ms, statistics.median(pub_ms)])
     return {"step_ms_alone": vals[0], "step_ms_with_publications": vals[1], "step_time_inflation": vals[1] / vals[0] - 1.0,
+            "eval_ms_lost_per_publication": (vals[1] - vals[0]) * 8,
             "weight_broadcast_overlapped_ms": vals[2], "publications": len(pub_ms), "every_n_steps": 8,
             "how": "rank 0's flat image + header broadcast (one NCCL collective) and fold / repack on a side stream of every rank "
                    "while the main stream evaluates; evaluations switch weight sets between calls (at_engine_publish_weights)"}
