@@ -53,6 +53,7 @@ EXPORTS = (
     "at_engine_submit_host",
     "at_engine_wait_host",
     "at_engine_last_launches",
+    "at_engine_set_kernel_timing",
     "at_engine_kernel_ms",
     "at_engine_bf16_trunk",
     "at_engine_action_dim",
@@ -132,6 +133,7 @@ def _bind(lib: C.CDLL) -> None:
         "at_engine_wait_host": (i32, [vp, i32]),
         "at_engine_last_launches": (i64, [vp]),
         "at_engine_bf16_trunk": (i32, [vp, vp, i64, vp, vp]),
+        "at_engine_set_kernel_timing": (i32, [vp, i32]),
         "at_engine_kernel_ms": (i32, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
         "at_engine_action_dim": (i32, [vp]),
         "at_probe_umma_ts": (i32, [vp, vp, i64, i32, i32, i32, u32, u32, u32, u32, u32, u32, vp, vp, vp]),

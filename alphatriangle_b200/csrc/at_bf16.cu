@@ -607,7 +607,7 @@ __global__ void __launch_bounds__(kFcThreads, 2) fc_kernel(const __grid_constant
 
 constexpr size_t tower_tf_smem_bytes() {
   return (size_t)kTfStages * kStageBytes + (size_t)kBoards * 2 * kBufBytes + kMaskBytes + (size_t)kMaxLayers * 128 * 4 + 9 * 128 * 4 +
-         128 * 4 + (size_t)kXchFloats * 4 + (2 * kStages + 4) * 8 + 16;
+         128 * 4 + (size_t)kXchFloats * 4 + (2 * kStages + 8) * 8 + 16;
 }
 
 }  // namespace
@@ -640,6 +640,7 @@ struct Bf16Path {
   int sms = 148;
   cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};  // tower begin/end, fc begin/end
   bool timed = false;
+  bool timing = false;  // record the event pairs around the tower / FC kernels (at_engine_set_kernel_timing): off on the serving path
   // transformer extension (tower_tf_kernel)
   bool tf = false;
   TowerTfParams ttp{};
@@ -768,16 +769,16 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
       for (int sl = 0; sl < tp.layers[l].n_slabs; ++sl) slab(tp.layers[l].slab_bytes);
     // the encoder's slabs in the order the issuers consume them (tower_tf_kernel, "encoder layers")
     for (int l = 0; l < d.t_layers; ++l) {
-      for (int h = 0; h < d.t_heads; ++h) {
-        if (h > 0) {
-          slab(kTfD * kTfDh * 2);                             // out_proj columns of head h-1
-          if (h == 1) bias_slab(kTfD);                        // out_proj bias
-        }
-        slab(3 * kTfDh * 64 * 2); slab(3 * kTfDh * 64 * 2);   // fused q|k|v projection of head h, two K halves
+      auto qkv_slabs = [&]() {
+        slab(3 * kTfDh * 64 * 2); slab(3 * kTfDh * 64 * 2);   // fused q|k|v projection of one head, two K halves
         bias_slab(3 * kTfDh);
+      };
+      qkv_slabs();                                            // head 0
+      for (int h = 0; h < d.t_heads; ++h) {
+        if (h + 1 < d.t_heads) qkv_slabs();                   // head h+1's projection is issued right behind head h's P V
+        slab(kTfD * kTfDh * 2);                               // out_proj columns of head h
+        if (h == 0) bias_slab(kTfD);                          // out_proj bias
       }
-      slab(kTfD * kTfDh * 2);
-      if (d.t_heads == 1) bias_slab(kTfD);
       for (int f = 0; f < t.ff_halves; ++f) {
         if (f > 0) {
           slab(128 * 64 * 2); slab(128 * 64 * 2);             // linear2, hidden half f-1
@@ -942,17 +943,17 @@ void bf16_add_prep_jobs(const Bf16Path* b, const Plan& p, PrepList& list) {
     const EncoderLayer& e = p.enc[l];
     const Sel out_all{kTfD, kTfD, 0, kTfD, kTfD, {0, 0, 0}, 1.0f};
     auto out_proj = [&](int h) { pack(e.out.wt, Sel{kTfD, kTfDh, h * kTfDh, kTfD, kTfD, {0, 0, 0}, 1.0f}, -1); };
-    for (int h = 0; h < d.t_heads; ++h) {
-      if (h > 0) {
-        out_proj(h - 1);
-        if (h == 1) bias(e.out.bias, -1, -1, out_all);
-      }
+    auto qkv_proj = [&](int h) {
       const Sel qkv{3 * kTfDh, kTfD, 0, 3 * kTfD, kTfDh, {h * kTfDh, kTfD + h * kTfDh, 2 * kTfD + h * kTfDh}, qscale};
       pack(e.qkv.wt, qkv, e.ln1_w);           // two ring slabs (K halves), contiguous
       bias(e.qkv.bias, e.qkv.wt, e.ln1_b, qkv);
+    };
+    qkv_proj(0);
+    for (int h = 0; h < d.t_heads; ++h) {
+      if (h + 1 < d.t_heads) qkv_proj(h + 1);
+      out_proj(h);
+      if (h == 0) bias(e.out.bias, -1, -1, out_all);
     }
-    out_proj(d.t_heads - 1);
-    if (d.t_heads == 1) bias(e.out.bias, -1, -1, out_all);
     auto linear2 = [&](int f) { pack(e.ff2.wt, Sel{kTfD, 128, f * 128, kTfD, kTfD, {0, 0, 0}, 1.0f}, -1); };
     for (int f = 0; f < halves; ++f) {
       if (f > 0) {
@@ -998,7 +999,7 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
 #endif
   const int64_t n_pairs = (batch + kBoards - 1) / kBoards;
   const unsigned grid = (unsigned)(n_pairs < b->sms ? n_pairs : b->sms);
-  AT_CUDA_TRY(cudaEventRecord(b->ev[0], st));
+  if (b->timing) AT_CUDA_TRY(cudaEventRecord(b->ev[0], st));
   if (b->tf) {
     TowerTfParams t = b->ttp;
     t.conv = tp;
@@ -1027,7 +1028,7 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
 #undef AT_TOWER_LAUNCH
   }
   AT_CUDA_TRY(cudaGetLastError());
-  AT_CUDA_TRY(cudaEventRecord(b->ev[1], st));
+  if (b->timing) AT_CUDA_TRY(cudaEventRecord(b->ev[1], st));
   ++*launches;
 
   // trunk FC: split-K. One CTA per SM (128 KB ring), so the launch runs in whole waves of `sms` CTAs: take the split count
@@ -1052,12 +1053,12 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
     }
   }
   FcParams fp{b->fc_a, b->wfc[slot], b->partial, batch, b->n_kc, b->fc_n, per, n_slabs, b->status, fmt};
-  AT_CUDA_TRY(cudaEventRecord(b->ev[2], st));
+  if (b->timing) AT_CUDA_TRY(cudaEventRecord(b->ev[2], st));
   fc_kernel<<<dim3((unsigned)m_tiles, (unsigned)splits), kFcThreads, fc_smem_bytes(), st>>>(fp);
   AT_CUDA_TRY(cudaGetLastError());
-  AT_CUDA_TRY(cudaEventRecord(b->ev[3], st));
+  if (b->timing) AT_CUDA_TRY(cudaEventRecord(b->ev[3], st));
   ++*launches;
-  b->timed = true;
+  b->timed = b->timing;
 
   *n_splits = splits;
   return AT_OK;
@@ -1087,9 +1088,10 @@ int bf16_finish_trunk(Bf16Path* b, const Plan& p, const float* folded, int slot,
 }
 
 const uint32_t* bf16_status_ptr(const Bf16Path* b) { return b->status; }
+void bf16_set_timing(Bf16Path* b, bool on) { b->timing = on; if (!on) b->timed = false; }
 
 int bf16_kernel_ms(Bf16Path* b, float* tower_ms, float* fc_ms) {
-  if (!b || !b->timed) return fail(AT_E_STATE, "no bf16 evaluation has run yet");
+  if (!b || !b->timed) return fail(AT_E_STATE, "no timed tensor-core evaluation has run yet (at_engine_set_kernel_timing)");
   AT_CUDA_TRY(cudaEventSynchronize(b->ev[3]));
   AT_CUDA_TRY(cudaEventElapsedTime(tower_ms, b->ev[0], b->ev[1]));
   AT_CUDA_TRY(cudaEventElapsedTime(fc_ms, b->ev[2], b->ev[3]));

@@ -40,6 +40,7 @@ int bf16_static_check(const Bf16Path* p, const Plan& plan, int64_t batch);  // b
 int bf16_trunk_partials_static(Bf16Path* p, const Plan& plan, const float* d_folded, int slot, const void* d_states, int64_t batch,
                                int* n_splits, const float** partial, const float** other, cudaStream_t stream, int64_t* launches);
 const uint32_t* bf16_status_ptr(const Bf16Path* p);  // device word: non-zero if a pipeline wait timed out
+void bf16_set_timing(Bf16Path* p, bool on);  // event pairs around the tower / FC kernels of every evaluation from now on
 int bf16_kernel_ms(Bf16Path* p, float* tower_ms, float* fc_ms);
 
 }  // namespace at

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <atomic>
 #include <string>
 
 #include "../../include/at_b200.h"
@@ -23,6 +24,20 @@ int fail(int code, const std::string& msg);
     cudaError_t _e = (expr);                                                                       \
     if (_e != cudaSuccess)                                                                         \
       return ::at::fail(AT_E_CUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));            \
+  } while (0)
+
+// Opt a kernel in to more than 48 KB of dynamic shared memory ONCE per device and call site (the attribute is per device;
+// setting it on every launch costs a driver call on the path trimcts drives with 32-leaf batches).
+#define AT_SMEM_OPT_IN_ONCE(kernel, bytes)                                                                        \
+  do {                                                                                                            \
+    static std::atomic<unsigned long long> done_{0};                                                              \
+    int dev_ = 0;                                                                                                 \
+    AT_CUDA_TRY(cudaGetDevice(&dev_));                                                                            \
+    const unsigned long long bit_ = 1ull << (dev_ & 63);                                                          \
+    if (!(done_.load(std::memory_order_acquire) & bit_)) {                                                        \
+      AT_CUDA_TRY(cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(bytes)));        \
+      done_.fetch_or(bit_, std::memory_order_release);                                                            \
+    }                                                                                                             \
   } while (0)
 
 #define AT_TRY(expr)              \

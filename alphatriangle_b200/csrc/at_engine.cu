@@ -564,6 +564,13 @@ int at_engine_supports(const at_engine* e, int precision) {
 int at_engine_action_dim(const at_engine* e) { return e ? e->plan.action_dim : 0; }
 int64_t at_engine_last_launches(const at_engine* e) { return e ? e->last_launches : 0; }
 
+int at_engine_set_kernel_timing(at_engine* e, int on) {
+  if (!e) return fail(AT_E_INVALID, "at_engine_set_kernel_timing: null engine");
+  if (!e->bf16) return fail(AT_E_UNSUPPORTED, "at_engine_set_kernel_timing: the tensor-core path is not available");
+  bf16_set_timing(e->bf16, on != 0);
+  return AT_OK;
+}
+
 int at_engine_kernel_ms(const at_engine* e, float* tower_ms, float* fc_ms) {
   if (!e || !tower_ms || !fc_ms) return fail(AT_E_INVALID, "at_engine_kernel_ms: null argument");
   if (!e->bf16) return fail(AT_E_UNSUPPORTED, "at_engine_kernel_ms: the bf16 path is not available");
@@ -695,6 +702,18 @@ int at_engine_evaluate_packed(at_engine* e, int precision, const void* d_states,
   return end_eval(e, st);
 }
 
+// Device-visible address of a pinned (page-locked, mapped) host buffer, or null for pageable memory.
+static void* pinned_device_ptr(const void* h) {
+  cudaPointerAttributes a;
+  if (cudaPointerGetAttributes(&a, h) != cudaSuccess) {
+    cudaGetLastError();
+    return nullptr;
+  }
+  return a.type == cudaMemoryTypeHost ? a.devicePointer : nullptr;
+}
+
+constexpr int64_t kZeroCopyMaxBatch = 256;
+
 int at_engine_evaluate_host(at_engine* e, int precision, const void* h_states, int64_t batch, float* h_policy, float* h_value,
                             uint32_t* h_flags, void* stream) {
   if (!e) return fail(AT_E_INVALID, "at_engine_evaluate_host: null engine");
@@ -705,6 +724,21 @@ int at_engine_evaluate_host(at_engine* e, int precision, const void* h_states, i
   if (!h_states || !h_policy || !h_value || !h_flags) return fail(AT_E_INVALID, "at_engine_evaluate_host: null pointer");
   DeviceGuard guard(e->device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (batch <= kZeroCopyMaxBatch) {
+    // The leaf batches one search sends (<= 32 states by default, mcts_config.py:14) are latency-, not bandwidth-bound: with
+    // pinned host buffers the kernels read the records and write probabilities / values straight through PCIe, which
+    // removes three copy-engine round trips from the call. Only the 4-byte status word is still copied.
+    void* ds = pinned_device_ptr(h_states);
+    void* dp = pinned_device_ptr(h_policy);
+    void* dv = pinned_device_ptr(h_value);
+    if (ds && dp && dv && (reinterpret_cast<uintptr_t>(ds) & 15u) == 0) {
+      AT_CUDA_TRY(cudaMemsetAsync(e->d_flags, 0, sizeof(uint32_t), st));
+      AT_TRY(at_engine_evaluate_packed(e, precision, ds, batch, static_cast<float*>(dp), static_cast<float*>(dv), e->d_flags, stream));
+      AT_CUDA_TRY(cudaMemcpyAsync(h_flags, e->d_flags, sizeof(uint32_t), cudaMemcpyDeviceToHost, st));
+      AT_CUDA_TRY(cudaStreamSynchronize(st));
+      return AT_OK;
+    }
+  }
   AT_CUDA_TRY(cudaMemcpyAsync(e->d_states, h_states, (size_t)batch * AT_STATE_BYTES, cudaMemcpyHostToDevice, st));
   AT_CUDA_TRY(cudaMemsetAsync(e->d_flags, 0, sizeof(uint32_t), st));
   // Slices: the device->host copy of slice i (5.9 MB per 4096 states) overlaps the kernels of slice i+1. Only worth it

@@ -266,7 +266,7 @@ int launch_features(const at_env_desc& env, int grid_channels, int other_dim, co
                        ((kFastThreads * other_dim) % 4 == 0) && ((grid_channels * env.rows * env.cols) % 4 == 0);
     const size_t smem = (size_t)kFastThreads * (sizeof(PackedState) + (size_t)other_dim * sizeof(float));
     if (smem <= 200 * 1024) {
-      if (smem > 48 * 1024) AT_CUDA_TRY(cudaFuncSetAttribute(features_fast_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      if (smem > 48 * 1024) AT_SMEM_OPT_IN_ONCE(features_fast_kernel, 200 * 1024);
       const int64_t fblocks = (batch + kFastThreads - 1) / kFastThreads;
       features_fast_kernel<<<(unsigned)fblocks, kFastThreads, smem, stream>>>(static_cast<const PackedState*>(d_states), batch, env.rows,
                                                                               env.cols, env.slots, grid_channels, other_dim, vec_ok,

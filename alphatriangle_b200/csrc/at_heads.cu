@@ -546,7 +546,7 @@ int launch_heads_fused(const HeadsParams& p, cudaStream_t stream, int64_t* launc
   HeadsParams q = p;
   q.w_stage_off = (int)act_floats(p);
   const size_t smem = heads_fused_smem(p);
-  AT_CUDA_TRY(cudaFuncSetAttribute(heads_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+  AT_SMEM_OPT_IN_ONCE(heads_fused_kernel, 200 * 1024);
   heads_fused_kernel<<<(unsigned)((q.batch + TB - 1) / TB), kThreads, smem, stream>>>(q);
   AT_CUDA_TRY(cudaGetLastError());
   if (launches) ++*launches;
@@ -597,10 +597,9 @@ int launch_heads_mma(const HeadsParams& p, cudaStream_t stream, int64_t* launche
   if (!p.states && !p.other) return fail(AT_E_INVALID, "launch_heads_mma: neither other features nor packed states given");
   const size_t smem = heads_mma_smem(p);
   const unsigned grid = (unsigned)((p.batch + TB - 1) / TB);
-  // the opt-in is per device and cheap; set on every launch so several engines on different GPUs stay correct
 #define AT_HEADS_LAUNCH(KT_, FMT_)                                                                                              \
   do {                                                                                                                          \
-    AT_CUDA_TRY(cudaFuncSetAttribute(heads_mma_kernel<KT_, FMT_>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));    \
+    AT_SMEM_OPT_IN_ONCE((heads_mma_kernel<KT_, FMT_>), 100 * 1024);                                                             \
     heads_mma_kernel<KT_, FMT_><<<grid, kMmaThreads, smem, stream>>>(p);                                                        \
   } while (0)
   if (mma_kt(p) == 8) {

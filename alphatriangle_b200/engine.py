@@ -213,8 +213,13 @@ class Engine:
         b = self._slot_batch[slot]
         return h_policy[:b].numpy(), h_value[:b].numpy(), int(h_flags[0].item())
 
+    def set_kernel_timing(self, on: bool) -> None:
+        """Record event pairs around the tower / FC kernels of the evaluations that follow (off by default)."""
+        _lib.check(self.lib.at_engine_set_kernel_timing(self.handle, 1 if on else 0), "at_engine_set_kernel_timing")
+
     def kernel_times(self) -> dict | None:
-        """Device milliseconds of the tower and FC kernels of the last bf16 evaluation (waits for it)."""
+        """Device milliseconds of the tower and FC kernels of the last tensor-core evaluation (waits for it); needs
+        set_kernel_timing(True) before that evaluation."""
         t, f = C.c_float(), C.c_float()
         rc = self.lib.at_engine_kernel_ms(self.handle, C.byref(t), C.byref(f))
         if rc != _lib.AT_OK:

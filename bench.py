@@ -358,6 +358,7 @@ class Workload:
         tower, fc = [], []
         if self.nn.precision not in self._lib.TENSOR_CORE_PRECISIONS:
             return None
+        self.nn.engine.set_kernel_timing(True)  # only for this pass: the timed steps above run without the extra events
         for i in range(steps):
             flush.fill_(i & 0xFF)
             self.step()
@@ -365,6 +366,7 @@ class Workload:
             if kt:
                 tower.append(kt["tower_ms"])
                 fc.append(kt["fc_ms"])
+        self.nn.engine.set_kernel_timing(False)
         if not tower:
             return None
         return {"tower_ms": sum(tower) / len(tower), "fc_ms": sum(fc) / len(fc)}

@@ -180,7 +180,9 @@ int at_engine_evaluate_packed_static(at_engine* e, const void* d_states, int64_t
 
 /* Same with HOST buffers (pinned memory recommended): copies the states in,
  * evaluates, copies probs / values / flags out and waits. This is the call a
- * host application (trimcts-style batcher) makes. */
+ * host application (trimcts-style batcher) makes. Batches of up to 256 states in
+ * pinned buffers skip the copies: the kernels read the records and write the
+ * results through PCIe directly (the latency path of a single search's <= 32 leaves). */
 int at_engine_evaluate_host(at_engine* e, int precision, const void* h_states, int64_t batch, float* h_policy, float* h_value,
                             uint32_t* h_flags, void* stream);
 
@@ -200,6 +202,9 @@ int at_engine_wait_host(at_engine* e, int slot);
  * device time (CUDA events on the launching stream) of the two tcgen05 kernels of the
  * last bf16 evaluation; waits for that evaluation to finish. */
 int64_t at_engine_last_launches(const at_engine* e);
+/* Kernel timing is off by default (four event records per call that the serving path does not need): switch it on before the
+ * evaluations at_engine_kernel_ms is asked about. */
+int at_engine_set_kernel_timing(at_engine* e, int on);
 int at_engine_kernel_ms(const at_engine* e, float* tower_ms, float* fc_ms);
 #define AT_FLAG_PIPELINE_TIMEOUT 0x80000000u /* a tcgen05 pipeline wait timed out (bits 8..15: which) */
 int at_engine_action_dim(const at_engine* e);

@@ -143,6 +143,8 @@ def test_bf16_through_the_drop_in_api(golden_dir):
     mc, env, _seed, g = load_case("conv_only", golden_dir)
     nn = network("conv_only", "bf16")
     states = case_states("conv_only", env)[:16]
+    assert nn.engine.kernel_times() is None or True  # timing is opt-in
+    nn.engine.set_kernel_timing(True)
     res = nn.evaluate_batch(states)
     for i, (pol, val) in enumerate(res):
         row = np.array([pol[a] for a in range(nn.action_dim)])
@@ -151,6 +153,7 @@ def test_bf16_through_the_drop_in_api(golden_dir):
         assert abs(val - float(g["values"][i])) <= VALUE_TOL["plain"]
     t = nn.engine.kernel_times()
     assert t is not None and t["tower_ms"] > 0 and t["fc_ms"] > 0
+    nn.engine.set_kernel_timing(False)
 
 
 # Head shapes that leave the tensor-core head kernel: (ModelConfig overrides, kernels expected after the tower and the FC)

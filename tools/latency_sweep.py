@@ -18,12 +18,16 @@ from alphatriangle_b200.packing import pack_states  # noqa: E402
 from alphatriangle_b200.synth import synth_state_dict, synth_states  # noqa: E402
 
 env = at.EnvConfig()
-base = pack_states(synth_states(256, env, seed=5), env)
+states = synth_states(256, env, seed=5)
+base = pack_states(states, env)
 for workload in ("conv_only", "default_tf"):
     mc = at.ModelConfig(USE_TRANSFORMER=(workload == "default_tf"))
-    nn = at.NeuralNetwork(mc, env, None, torch.device("cuda:0"), precision="bf16", max_batch=16384)
+    nn = at.NeuralNetwork(mc, env, None, torch.device("cuda:0"), precision="auto", max_batch=16384)
     nn.set_weights(synth_state_dict(nn.get_weights(), 1))
     nn._sync_engine()
+    from alphatriangle_b200 import _lib  # noqa: E402
+
+    prec = _lib.PRECISION_NAMES[nn.precision]
     for B in (1, 8, 32, 128, 296, 512, 1024, 2048, 4096, 8192, 16384):
         packed_h = np.tile(base, (-(-B // 256), 1))[:B]
         packed_d = torch.from_numpy(packed_h).cuda()
@@ -44,6 +48,17 @@ for workload in ("conv_only", "default_tf"):
             t0 = time.perf_counter()
             nn.engine.evaluate_host(packed_h, nn.precision)
             host_ms.append((time.perf_counter() - t0) * 1e3)
-        print(json.dumps({"workload": workload, "batch": B, "device_p50_ms": statistics.median(dev_ms),
-                          "host_call_p50_ms": statistics.median(host_ms), "states_per_s_device": B / (statistics.median(dev_ms) * 1e-3)}))
+        row = {"workload": workload, "precision": prec, "batch": B, "device_p50_ms": statistics.median(dev_ms),
+               "host_call_p50_ms": statistics.median(host_ms), "states_per_s_device": B / (statistics.median(dev_ms) * 1e-3)}
+        if B <= 128:  # what trimcts calls: evaluate_batch on state objects (packing, version check, kernels, result dicts)
+            sts = (states * (-(-B // len(states))))[:B]
+            api_ms = []
+            for _ in range(3):
+                nn.evaluate_batch(sts)
+            for _ in range(reps):
+                t0 = time.perf_counter()
+                nn.evaluate_batch(sts)
+                api_ms.append((time.perf_counter() - t0) * 1e3)
+            row["evaluate_batch_p50_ms"] = statistics.median(api_ms)
+        print(json.dumps(row), flush=True)
     del nn

@@ -20,6 +20,7 @@ nn = at.NeuralNetwork(mc, env, None, torch.device("cuda:0"), precision=os.enviro
 nn.set_weights(synth_state_dict(nn.get_weights(), 1))
 base = pack_states(synth_states(256, env, seed=5), env)
 packed = torch.from_numpy(np.tile(base, (-(-B // 256), 1))[:B]).cuda()
+nn.engine.set_kernel_timing(True)
 ts = []
 for _ in range(reps):
     probs, value, _flags = nn.engine.evaluate_packed(packed, nn.precision)
