@@ -157,22 +157,50 @@ __device__ void job_bias_slab(const PrepJob& j, const PrepBases& b, int fmt, int
 // a: bias, Wt, beta (folded floats)   i: K, N, period.   One block; thread (n, part) sums a K range, parts combined in shared memory.
 __device__ void job_fc_bias(const PrepJob& j, const PrepBases& b, int rank, int nb) {
   if (rank != 0) return;
-  __shared__ float part[256];
+  __shared__ float4 part[256];
   const float* __restrict__ folded = static_cast<const float*>(b.p[PB_FOLDED]);
-  const float* __restrict__ wt = folded + j.a[1];
+  const float4* __restrict__ wt4 = reinterpret_cast<const float4*>(folded + j.a[1]);  // 16-byte aligned: reserve() keeps it so
   const float* __restrict__ beta = folded + j.a[2];
   float* __restrict__ out = static_cast<float*>(b.p[PB_FCBIAS]);
   const int K = j.i[0], N = j.i[1], period = j.i[2];
-  const int parts = 256 / N > 0 ? 256 / N : 1;  // N <= 128 on this path
-  const int n = threadIdx.x % N, part_id = threadIdx.x / N;
-  float acc = 0.0f;
-  if (part_id < parts)
-    for (int k = part_id; k < K; k += parts) acc = fmaf(wt[(size_t)k * N + n], beta[k % period], acc);
-  part[threadIdx.x] = part_id < parts ? acc : 0.0f;
+  const int n4 = N / 4;                          // N is a multiple of 32 on this path: thread = (4 columns, K part)
+  const int parts = 256 / n4;
+  const int g = threadIdx.x % n4, part_id = threadIdx.x / n4;
+  // a chain of L2 loads otherwise: float4 columns, eight rows in flight
+  float4 acc[8];
+#pragma unroll
+  for (int u = 0; u < 8; ++u) acc[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (part_id < parts) {
+    int k = part_id;
+    for (; k + 7 * parts < K; k += 8 * parts) {
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int kk = k + u * parts;
+        const float4 w = __ldg(wt4 + (size_t)kk * n4 + g);
+        const float bt = beta[kk % period];
+        acc[u].x = fmaf(w.x, bt, acc[u].x); acc[u].y = fmaf(w.y, bt, acc[u].y);
+        acc[u].z = fmaf(w.z, bt, acc[u].z); acc[u].w = fmaf(w.w, bt, acc[u].w);
+      }
+    }
+    for (; k < K; k += parts) {
+      const float4 w = __ldg(wt4 + (size_t)k * n4 + g);
+      const float bt = beta[k % period];
+      acc[0].x = fmaf(w.x, bt, acc[0].x); acc[0].y = fmaf(w.y, bt, acc[0].y);
+      acc[0].z = fmaf(w.z, bt, acc[0].z); acc[0].w = fmaf(w.w, bt, acc[0].w);
+    }
+  }
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+  for (int u = 0; u < 8; ++u) { s.x += acc[u].x; s.y += acc[u].y; s.z += acc[u].z; s.w += acc[u].w; }
+  part[threadIdx.x] = part_id < parts ? s : make_float4(0.f, 0.f, 0.f, 0.f);
   __syncthreads();
   if (threadIdx.x < N) {
+    const int gg = threadIdx.x / 4, c = threadIdx.x % 4;
     float v = folded[j.a[0] + threadIdx.x];
-    for (int q = 0; q < parts; ++q) v += part[q * N + threadIdx.x];
+    for (int q = 0; q < parts; ++q) {
+      const float4 t = part[q * n4 + gg];
+      v += c == 0 ? t.x : (c == 1 ? t.y : (c == 2 ? t.z : t.w));
+    }
     out[threadIdx.x] = v;
   }
 }

@@ -505,7 +505,7 @@ def measure_publication(w, steps, flush):
     pub.publish(src=0)
     pub.wait()
     w.barrier()
-    n = max(steps, 10) * 4
+    n, every = 160, 32
 
     def timed(with_pub):
         begin, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -514,7 +514,7 @@ def measure_publication(w, steps, flush):
         w.barrier()
         begin.record()
         for i in range(n):
-            if with_pub and i % 8 == 2:  # every rank takes part in the collective; the main stream never waits for it
+            if with_pub and i % every == 2:  # every rank takes part in the collective; the main stream never waits for it
                 p0 = torch.cuda.Event(enable_timing=True)
                 p1 = torch.cuda.Event(enable_timing=True)
                 p0.record(pub.stream)
@@ -531,10 +531,21 @@ def measure_publication(w, steps, flush):
     base_ms, _ = timed(False)
     with_ms, pub_ms = timed(True)
     w.check_flags("the publication run")
+    # after the last publication every rank must hold rank 0's weights: the same probe batch gives the same bits everywhere
+    from alphatriangle_b200.packing import pack_states
+    from alphatriangle_b200.synth import synth_states
+
+    probe = torch.from_numpy(pack_states(synth_states(256, w.nn.env_config, seed=4242), w.nn.env_config)).to(w.dev)
+    pp, pv, _pf = w.nn.engine.evaluate_packed(probe, w.nn.precision)
+    digest = torch.stack([pp.view(torch.int32).sum(dtype=torch.int64), pv.view(torch.int32).sum(dtype=torch.int64)])
+    digests = [torch.zeros_like(digest) for _ in range(w.world)]
+    torch.distributed.all_gather(digests, digest)
+    identical = all(bool(torch.equal(d, digests[0])) for d in digests)
     vals = reduce_max(torch, w.dev, w.world, [base_ms, with_ms, statistics.median(pub_ms)])
     return {"step_ms_alone": vals[0], "step_ms_with_publications": vals[1], "step_time_inflation": vals[1] / vals[0] - 1.0,
-            "eval_ms_lost_per_publication": (vals[1] - vals[0]) * 8,
-            "weight_broadcast_overlapped_ms": vals[2], "publications": len(pub_ms), "every_n_steps": 8,
+            "eval_ms_lost_per_publication": (vals[1] - vals[0]) * every,
+            "weight_broadcast_overlapped_ms": vals[2], "publications": len(pub_ms), "every_n_steps": every,
+            "replicas_bit_identical_after_publication": identical,
             "how": "rank 0's flat image + header broadcast (one NCCL collective) and fold / repack on a side stream of every rank "
                    "while the main stream evaluates; evaluations switch weight sets between calls (at_engine_publish_weights)"}
 
