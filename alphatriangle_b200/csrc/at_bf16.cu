@@ -63,8 +63,23 @@ constexpr long long kTimeoutCycles = 2000000000LL;  // ~1 s: a wedged pipeline r
 // library the tests below are compile-time false and the environment is never read.
 #ifdef AT_EXPERIMENTS
 #define AT_DBG(bits) ((p.debug & (bits)) != 0)
+// Timeline of one board pair in CTA 0 (experiments build only): every warp's lane 0 stamps clock64() at named points into
+// g_timeline[warp][event]; tools/tower_timeline.py prints them relative to the pair's start (at_debug_read_timeline).
+constexpr int kTlEvents = 96;
+__device__ unsigned long long g_timeline[32 * kTlEvents];
+#define AT_TL_DECL int tl_i = 0; bool tl_on = false;
+#define AT_TL_PAIR(pair) tl_on = (blockIdx.x == 0 && (pair) == (int64_t)3 * gridDim.x); tl_i = 0;
+#define AT_TL(tag)                                                                                              \
+  do {                                                                                                          \
+    if (tl_on && (threadIdx.x & 31) == 0 && tl_i < kTlEvents) {                                                 \
+      g_timeline[(threadIdx.x >> 5) * kTlEvents + tl_i++] = ((unsigned long long)(tag) << 48) | (clock64() & 0xFFFFFFFFFFFFull); \
+    }                                                                                                           \
+  } while (0)
 #else
 #define AT_DBG(bits) false
+#define AT_TL_DECL
+#define AT_TL_PAIR(pair)
+#define AT_TL(tag)
 #endif
 
 struct TowerLayer {
@@ -295,9 +310,12 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     if (lane == 0 && use_ring) {
       uint32_t stage = 0, phase = 0;
       bool ok = true;
+      AT_TL_DECL
       for (int64_t pair = pair0; pair < n_pairs && ok; pair += gridDim.x) {
+        AT_TL_PAIR(pair)
         const uint8_t* src = p.wstream;
         for (int l = 0; l < p.n_layers && ok; ++l) {
+          AT_TL(100 + l);
           const uint32_t bytes = p.layers[l].slab_bytes;
           const int n_slabs = p.layers[l].n_slabs;
           for (int s = 0; s < n_slabs; ++s) {
@@ -327,11 +345,15 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     const bool no_mma = AT_DBG(2u);
     uint32_t stage = 0, phase = 0, lphase = 0;
     bool ok = true;
+    AT_TL_DECL
     for (int64_t pair = pair0; pair < n_pairs && ok; pair += gridDim.x) {
+      AT_TL_PAIR(pair)
+      AT_TL(1);
       for (int l = 0; l < p.n_layers && ok; ++l) {
         const TowerLayer& L = p.layers[l];
         ok = __all_sync(0xffffffffu, wait_bar(my_act, lphase, p.status, 2u));  // this layer's input image is written
         if (!ok) break;
+        AT_TL(10 + l);  // input image ready
         lphase ^= 1u;
         tc_fence_after();
         const uint32_t idesc = idesc_16(kM, (uint32_t)L.cout, FMT == FMT_BF16);
@@ -368,6 +390,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         }
         if (ok && elect_one()) mma_commit(my_acc);
         __syncwarp();
+        AT_TL(30 + l);  // last slab issued, accumulator committed
       }
     }
   } else {
@@ -391,7 +414,10 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
       __syncwarp();
       if (lane == 0) mbar_arrive(my_act);
     };
+    AT_TL_DECL
     for (int64_t pair = pair0; pair < n_pairs && ok; pair += gridDim.x) {
+      AT_TL_PAIR(pair)
+      AT_TL(1);
       const int64_t board = pair * kBoards + eb;
       const bool valid = board < p.batch;
       // The previous board's last epilogue may still be reading its residual from image 0 in the sibling warp (other
@@ -429,11 +455,13 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         }
       }
       arrive_act();
+      AT_TL(2);  // layer 0 written
 
       for (int l = 0; l < p.n_layers; ++l) {
         const TowerLayer& L = p.layers[l];
         ok = wait_bar(my_acc, acc_phase, p.status, 8u);
         if (!ok) break;
+        AT_TL(50 + l);  // accumulator seen complete
         acc_phase ^= 1;
         tc_fence_after();
         const float* bias = s_bias + L.bias_slot * 128;
@@ -481,6 +509,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         }
         tc_fence_before();  // TMEM reads are done before the next layer's MMAs overwrite the accumulator
         if (l + 1 < p.n_layers) arrive_act();
+        AT_TL(70 + l);  // drained, next image posted
       }
     }
   }
@@ -1189,5 +1218,14 @@ int bf16_trunk_partials_static(Bf16Path* b, const Plan& p, const float* folded, 
   b->grid = keep_grid;
   return rc;
 }
+
+#ifdef AT_EXPERIMENTS
+int debug_read_timeline(unsigned long long* out, int n) {
+  if (n > 32 * kTlEvents) n = 32 * kTlEvents;
+  AT_CUDA_TRY(cudaDeviceSynchronize());
+  AT_CUDA_TRY(cudaMemcpyFromSymbol(out, g_timeline, (size_t)n * sizeof(unsigned long long)));
+  return n;
+}
+#endif
 
 }  // namespace at

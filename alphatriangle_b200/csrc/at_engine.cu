@@ -812,3 +812,8 @@ int at_engine_wait_host(at_engine* e, int slot) {
 }
 
 }  // extern "C"
+
+#ifdef AT_EXPERIMENTS
+namespace at { int debug_read_timeline(unsigned long long* out, int n); }
+extern "C" int at_debug_read_timeline(unsigned long long* out, int n) { return at::debug_read_timeline(out, n); }
+#endif
