@@ -47,7 +47,15 @@ constexpr int kPlaneBytes = kPlaneRows * 16; // 2,320
 constexpr int kMaxCh = 128;
 constexpr int kBufBytes = (kMaxCh / 8) * kPlaneBytes + kHalo * 16;  // 37,392: 16 planes + the last plane's trailing halo
 constexpr int kStageBytes = 16384;
-constexpr int kStages = 4;
+// AT_TOWER_OVERLAP = 1: the next pair's first image is produced before the current pair's last accumulator is drained (image
+// buffers and accumulators swap roles from pair to pair), so the tensor pipe restarts ~10k cycles earlier per pair.
+#ifndef AT_TOWER_OVERLAP
+#define AT_TOWER_OVERLAP 1
+#endif
+#ifndef AT_TOWER_STAGES
+#define AT_TOWER_STAGES 4
+#endif
+constexpr int kStages = AT_TOWER_STAGES;  // weight ring depth of tower_kernel
 constexpr int kMaxLayers = 12;
 constexpr int kMaxSlabs = 36;                // weight slabs per layer (9 taps x 128 channels / 64 = 18 at the defaults)
 constexpr int kBoards = 2;                   // boards in flight per CTA
@@ -55,6 +63,7 @@ constexpr int kEpiSplit = 2;                 // epilogue warps per (board, TMEM 
 constexpr int kEpiWarps = kBoards * 4 * kEpiSplit;
 constexpr int kMmaWarpB = 2 + kEpiWarps;      // MMA-issuing warp of board 1; warp 1 issues for board 0
 constexpr int kTowerThreads = 64 + kEpiWarps * 32 + 32;
+constexpr int kTowerTmemCols = AT_TOWER_OVERLAP ? 512 : kBoards * 128;  // per board one accumulator, or two used by alternate pairs
 constexpr int kMaxBars = 32;                 // mbarrier slots reserved in shared memory
 constexpr long long kTimeoutCycles = 2000000000LL;  // ~1 s: a wedged pipeline reports instead of hanging
 
@@ -291,7 +300,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     fence_mbar_init();
   }
   if (warp == 0) {
-    tmem_alloc(smem_u32(tmem_slot), kBoards * 128);
+    tmem_alloc(smem_u32(tmem_slot), kTowerTmemCols);
     tmem_relinquish();
   }
   fence_proxy_async_smem();  // the zeroed halos are read by the tensor core (async proxy)
@@ -328,7 +337,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
               bulk_g2s(ring_u + stage * SB, src, bytes, bar_full + 8 * stage);
             }
             src += bytes;
-            stage = (stage + 1) & (NS - 1);
+            stage = stage + 1 == NS ? 0 : stage + 1;
             phase ^= (stage == 0);
           }
         }
@@ -340,8 +349,9 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     // skeleton without MMAs runs 20 % faster -- but the full kernel is 1.5 % slower with it.)
     const int me = warp == 1 ? 0 : 1;
     const uint32_t my_acc = me == 0 ? bar_acc0 : bar_acc1, my_act = me == 0 ? bar_act0 : bar_act1;
-    const uint32_t tmem_d = tmem_base + (uint32_t)me * 128;
+    const uint32_t tmem_d0 = tmem_base + (uint32_t)me * 128;
     const uint32_t a_lo_fixed = (uint32_t)(kPlaneBytes >> 4) << 16;  // LBO = one 8-channel plane
+    uint32_t par = 0;  // pair parity: which of the two image buffers is "buffer 0" and which accumulator is in use
     const bool no_mma = AT_DBG(2u);
     uint32_t stage = 0, phase = 0, lphase = 0;
     bool ok = true;
@@ -349,6 +359,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     for (int64_t pair = pair0; pair < n_pairs && ok; pair += gridDim.x) {
       AT_TL_PAIR(pair)
       AT_TL(1);
+      const uint32_t tmem_d = tmem_d0 + par * 256u;
       for (int l = 0; l < p.n_layers && ok; ++l) {
         const TowerLayer& L = p.layers[l];
         ok = __all_sync(0xffffffffu, wait_bar(my_act, lphase, p.status, 2u));  // this layer's input image is written
@@ -358,7 +369,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         tc_fence_after();
         const uint32_t idesc = idesc_16(kM, (uint32_t)L.cout, FMT == FMT_BF16);
         // descriptor low words: [13:0] start address >> 4, [29:16] LBO >> 4; the address sums below stay inside 14 bits
-        const uint32_t a_base = a_lo_fixed | ((act_u + (uint32_t)(me * 2 + L.src) * kBufBytes) >> 4);
+        const uint32_t a_base = a_lo_fixed | ((act_u + (uint32_t)(me * 2 + ((uint32_t)L.src ^ par)) * kBufBytes) >> 4);
         const uint32_t b_base = ((uint32_t)L.cout << 16) | (ring_u >> 4);  // LBO = one 8-channel plane of the slab (Cout rows of 16 B)
         const uint32_t b_step = 2u * (uint32_t)L.cout;                      // one K-step = two planes
         const int n_slabs = L.n_slabs;
@@ -385,13 +396,14 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
             if (use_ring) mma_commit(bar_empty + 8 * stage);  // the slab may be overwritten once these MMAs retire
           }
           __syncwarp();
-          stage = (stage + 1) & (NS - 1);
+          stage = stage + 1 == NS ? 0 : stage + 1;
           phase ^= (stage == 0);
         }
         if (ok && elect_one()) mma_commit(my_acc);
         __syncwarp();
         AT_TL(30 + l);  // last slab issued, accumulator committed
       }
+      if (AT_TOWER_OVERLAP) par ^= 1u;
     }
   } else {
     // ===== epilogue warps: 8 per board; warp%4 selects the TMEM lane quarter =====
@@ -404,8 +416,8 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     const uint32_t keep = inside ? 0xFFFFFFFFu : 0u;
     const int pos = y * p.cols + x;  // compact position index (token order h*W + w)
     const uint32_t my_act_u = act_u + (uint32_t)eb * 2 * kBufBytes + (uint32_t)(kHalo + m) * 16;  // this row, plane 0, buffer 0
-    const uint32_t tmem_row = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)eb * 128;
-    uint32_t acc_phase = 0;
+    const uint32_t tmem_row0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)eb * 128;
+    uint32_t acc_phase = 0, par = 0;
     bool ok = true;
     const uint32_t my_act = eb == 1 ? bar_act1 : bar_act0;
     const uint32_t my_acc = eb == 1 ? bar_acc1 : bar_acc0;
@@ -414,61 +426,100 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
       __syncwarp();
       if (lane == 0) mbar_arrive(my_act);
     };
+    // ---- layer 0 on CUDA cores, straight from the bitmasks (extractor.py:33-46 + conv_body.0): this thread's position,
+    // channels eh*8 + 16*i .. +7. Either kept in registers (c0 <= 16 * kL0Keep) or written to the image `dst_buf` at once.
+    constexpr int kL0Keep = 2;
+    auto layer0 = [&](int64_t board, bool valid, uint4 (&keepv)[kL0Keep], bool to_regs, uint32_t dst_buf) {
+      if (AT_DBG(8u)) return;
+      float g[9];
+#pragma unroll
+      for (int t = 0; t < 9; ++t) g[t] = 0.0f;
+      if (valid) {
+        const PackedState& st = p.states[board];
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+          const int yy = y + t / 3 - 1, xx = x + t % 3 - 1;
+          if (yy >= 0 && yy < p.rows && xx >= 0 && xx < p.cols) {
+            const int i = yy * p.cols + xx;
+            const uint32_t bit = 1u << (i & 31);
+            g[t] = (st.death[i >> 5] & bit) ? -1.0f : ((st.occ[i >> 5] & bit) ? 1.0f : 0.0f);
+          }
+        }
+      }
+      auto one = [&](int c8) {
+        const float4 ba = *reinterpret_cast<const float4*>(s_b0 + c8), bb = *reinterpret_cast<const float4*>(s_b0 + c8 + 4);
+        float v[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
+#pragma unroll
+        for (int t = 0; t < 9; ++t) {
+          const float4 wa = *reinterpret_cast<const float4*>(s_w0 + t * p.c0 + c8);
+          const float4 wb = *reinterpret_cast<const float4*>(s_w0 + t * p.c0 + c8 + 4);
+          v[0] = fmaf(g[t], wa.x, v[0]); v[1] = fmaf(g[t], wa.y, v[1]); v[2] = fmaf(g[t], wa.z, v[2]); v[3] = fmaf(g[t], wa.w, v[3]);
+          v[4] = fmaf(g[t], wb.x, v[4]); v[5] = fmaf(g[t], wb.y, v[5]); v[6] = fmaf(g[t], wb.z, v[6]); v[7] = fmaf(g[t], wb.w, v[7]);
+        }
+        return pack8_act<ACT, FMT>(v, keep);
+      };
+      if (to_regs) {
+#pragma unroll
+        for (int i = 0; i < kL0Keep; ++i) {
+          const int c8 = eh * 8 + i * 8 * kEpiSplit;
+          keepv[i] = c8 < p.c0 ? one(c8) : make_uint4(0, 0, 0, 0);
+        }
+      } else {
+#pragma unroll 1
+        for (int c8 = eh * 8; c8 < p.c0; c8 += 8 * kEpiSplit) sts128(my_act_u + dst_buf * kBufBytes + (uint32_t)(c8 / 8) * kPlaneBytes, one(c8));
+      }
+    };
+    auto store_layer0 = [&](const uint4 (&keepv)[kL0Keep], uint32_t dst_buf) {
+#pragma unroll
+      for (int i = 0; i < kL0Keep; ++i) {
+        const int c8 = eh * 8 + i * 8 * kEpiSplit;
+        if (c8 < p.c0) sts128(my_act_u + dst_buf * kBufBytes + (uint32_t)(c8 / 8) * kPlaneBytes, keepv[i]);
+      }
+    };
+    const bool l0_in_regs = p.c0 <= 8 * kEpiSplit * kL0Keep;
+    uint4 l0v[kL0Keep];
     AT_TL_DECL
+    bool first = true;
     for (int64_t pair = pair0; pair < n_pairs && ok; pair += gridDim.x) {
       AT_TL_PAIR(pair)
       AT_TL(1);
       const int64_t board = pair * kBoards + eb;
       const bool valid = board < p.batch;
-      // The previous board's last epilogue may still be reading its residual from image 0 in the sibling warp (other
-      // channel share, same rows): all eight epilogue warps of this board finish it before anyone writes the new image.
-      if (!AT_DBG(64u)) asm volatile("bar.sync %0, %1;" ::"r"(1 + eb), "r"(kEpiWarps / kBoards * 32) : "memory");
-      // ---- layer 0 on CUDA cores, straight from the bitmasks (extractor.py:33-46 + conv_body.0) ----
-      if (!AT_DBG(8u)) {
-        float g[9];
-#pragma unroll
-        for (int t = 0; t < 9; ++t) g[t] = 0.0f;
-        if (valid) {
-          const PackedState& st = p.states[board];
-#pragma unroll
-          for (int t = 0; t < 9; ++t) {
-            const int yy = y + t / 3 - 1, xx = x + t % 3 - 1;
-            if (yy >= 0 && yy < p.rows && xx >= 0 && xx < p.cols) {
-              const int i = yy * p.cols + xx;
-              const uint32_t bit = 1u << (i & 31);
-              g[t] = (st.death[i >> 5] & bit) ? -1.0f : ((st.occ[i >> 5] & bit) ? 1.0f : 0.0f);
-            }
-          }
-        }
-#pragma unroll 1
-        for (int c8 = eh * 8; c8 < p.c0; c8 += 8 * kEpiSplit) {
-          const float4 ba = *reinterpret_cast<const float4*>(s_b0 + c8), bb = *reinterpret_cast<const float4*>(s_b0 + c8 + 4);
-          float v[8] = {ba.x, ba.y, ba.z, ba.w, bb.x, bb.y, bb.z, bb.w};
-#pragma unroll
-          for (int t = 0; t < 9; ++t) {
-            const float4 wa = *reinterpret_cast<const float4*>(s_w0 + t * p.c0 + c8);
-            const float4 wb = *reinterpret_cast<const float4*>(s_w0 + t * p.c0 + c8 + 4);
-            v[0] = fmaf(g[t], wa.x, v[0]); v[1] = fmaf(g[t], wa.y, v[1]); v[2] = fmaf(g[t], wa.z, v[2]); v[3] = fmaf(g[t], wa.w, v[3]);
-            v[4] = fmaf(g[t], wb.x, v[4]); v[5] = fmaf(g[t], wb.y, v[5]); v[6] = fmaf(g[t], wb.z, v[6]); v[7] = fmaf(g[t], wb.w, v[7]);
-          }
-          sts128(my_act_u + (uint32_t)(c8 / 8) * kPlaneBytes, pack8_act<ACT, FMT>(v, keep));
-        }
+      const uint32_t tmem_row = tmem_row0 + par * 256u;
+      if (!AT_TOWER_OVERLAP || first) {
+        // The previous board's last epilogue may still be reading its residual from image 0 in the sibling warp (other
+        // channel share, same rows): all eight epilogue warps of this board finish it before anyone writes the new image.
+        if (!AT_DBG(64u)) asm volatile("bar.sync %0, %1;" ::"r"(1 + eb), "r"(kEpiWarps / kBoards * 32) : "memory");
+        layer0(board, valid, l0v, false, par);
+        arrive_act();
+        first = false;
       }
-      arrive_act();
       AT_TL(2);  // layer 0 written
 
       for (int l = 0; l < p.n_layers; ++l) {
         const TowerLayer& L = p.layers[l];
+        // Overlap: while the last layer's MMAs run, work out the NEXT pair's layer 0 (registers); once they are done its
+        // source image -- the pair's scratch buffer -- is free, so the next pair's first image goes there and its MMAs start
+        // (on the other accumulator) while this pair's last accumulator is still being drained to HBM below.
+        const int64_t next_pair = pair + gridDim.x;
+        const bool hand_over = AT_TOWER_OVERLAP && l + 1 == p.n_layers && next_pair < n_pairs;
+        const int64_t next_board = next_pair * kBoards + eb;
+        if (hand_over && l0_in_regs) layer0(next_board, next_board < p.batch, l0v, true, 0);
         ok = wait_bar(my_acc, acc_phase, p.status, 8u);
         if (!ok) break;
         AT_TL(50 + l);  // accumulator seen complete
         acc_phase ^= 1;
         tc_fence_after();
+        if (hand_over) {
+          if (l0_in_regs) store_layer0(l0v, par ^ 1u);
+          else layer0(next_board, next_board < p.batch, l0v, false, par ^ 1u);
+          arrive_act();
+        }
         const float* bias = s_bias + L.bias_slot * 128;
         const bool has_res = L.res >= 0;
-        const uint32_t res_u = my_act_u + (uint32_t)(has_res ? L.res : 0) * kBufBytes;
+        const uint32_t res_u = my_act_u + ((uint32_t)(has_res ? L.res : 0) ^ par) * kBufBytes;
         const bool to_smem = L.dst < 2;
-        const uint32_t dst_u = my_act_u + (uint32_t)(to_smem ? L.dst : 0) * kBufBytes;
+        const uint32_t dst_u = my_act_u + ((uint32_t)(to_smem ? L.dst : 0) ^ par) * kBufBytes;
         uint8_t* gdst = p.fc_a + (((board >> 7) * p.n_kc + (int64_t)pos * (L.cout / 8)) * 128 + (board & 127)) * 16;
         const bool gstore = valid && inside;
         const int cout = AT_DBG(4u) ? 0 : L.cout;
@@ -511,12 +562,18 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         if (l + 1 < p.n_layers) arrive_act();
         AT_TL(70 + l);  // drained, next image posted
       }
+      if (AT_TOWER_OVERLAP) {
+        // the sibling warp (other channel share, same rows) may still read this pair's residual image, which the next pair's
+        // second layer overwrites: everyone finishes the drain first
+        if (!AT_DBG(64u)) asm volatile("bar.sync %0, %1;" ::"r"(1 + eb), "r"(kEpiWarps / kBoards * 32) : "memory");
+        par ^= 1u;
+      }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) tmem_dealloc(tmem_base, kBoards * 128);
+  if (warp == 0) tmem_dealloc(tmem_base, kTowerTmemCols);
 }
 
 // ---- trunk FC: split-K tcgen05 GEMM ---------------------------------------------------------
