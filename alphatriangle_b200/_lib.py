@@ -57,9 +57,6 @@ EXPORTS = (
     "at_engine_kernel_ms",
     "at_engine_bf16_trunk",
     "at_engine_action_dim",
-    "at_probe_umma",
-    "at_probe_umma_ts",
-    "at_probe_mma_rate",
 )
 
 
@@ -136,9 +133,6 @@ def _bind(lib: C.CDLL) -> None:
         "at_engine_set_kernel_timing": (i32, [vp, i32]),
         "at_engine_kernel_ms": (i32, [vp, C.POINTER(C.c_float), C.POINTER(C.c_float)]),
         "at_engine_action_dim": (i32, [vp]),
-        "at_probe_umma_ts": (i32, [vp, vp, i64, i32, i32, i32, u32, u32, u32, u32, u32, u32, vp, vp, vp]),
-        "at_probe_mma_rate": (i32, [i32, i32, i32, i32, i32, vp, i32, vp, vp]),
-        "at_probe_umma": (i32, [vp, i64, vp, i64, i32, i32, u32, u32, u32, u32, u32, u32, u32, u32, i32, vp, vp, vp]),
     }
     for name, (res, args) in sig.items():
         fn = getattr(lib, name)
@@ -162,6 +156,38 @@ def load() -> C.CDLL:
             raise LibraryError(f"{path}: ABI version {lib.at_abi_version()} != 1")
         _lib = lib
     return _lib
+
+
+# include/at_b200_probe.h: the bring-up probes live in their own library (tests/test_gpu_probe.py, tools/mma_rate.py)
+PROBE_LIB_PATH = Path(__file__).resolve().parent / "libat_b200_probe.so"
+PROBE_EXPORTS = ("at_probe_last_error", "at_probe_umma", "at_probe_umma_ts", "at_probe_mma_rate")
+_probe = None
+
+
+def load_probe() -> C.CDLL:
+    global _probe
+    if _probe is None:
+        if not PROBE_LIB_PATH.exists():
+            raise LibraryError(f"{PROBE_LIB_PATH} not found: build it with `python __graft_entry__.py build`")
+        lib = C.CDLL(str(PROBE_LIB_PATH))
+        vp, i32, i64, u32 = C.c_void_p, C.c_int, C.c_int64, C.c_uint32
+        lib.at_probe_last_error.restype = C.c_char_p
+        lib.at_probe_last_error.argtypes = []
+        for name, args in (
+            ("at_probe_umma_ts", [vp, vp, i64, i32, i32, i32, u32, u32, u32, u32, u32, u32, vp, vp, vp]),
+            ("at_probe_mma_rate", [i32, i32, i32, i32, i32, vp, i32, vp, vp]),
+            ("at_probe_umma", [vp, i64, vp, i64, i32, i32, u32, u32, u32, u32, u32, u32, u32, u32, i32, vp, vp, vp]),
+        ):
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = i32, args
+        _probe = lib
+    return _probe
+
+
+def check_probe(rc: int, what: str) -> None:
+    if rc != AT_OK:
+        msg = load_probe().at_probe_last_error()
+        raise LibraryError(f"{what} failed ({rc}): {msg.decode('utf-8', 'replace') if msg else ''}", rc)
 
 
 def last_error() -> str:

@@ -4,8 +4,22 @@
 // the descriptor conventions (core-matrix strides, row-shifted start addresses,
 // 128-byte swizzle) that the convolution tower depends on.
 
+#include "../../include/at_b200_probe.h"
 #include "at_common.cuh"
 #include "at_umma.cuh"
+
+// libat_b200_probe.so is linked on its own: it carries its own copy of the error plumbing at_common.cuh declares
+namespace at {
+namespace {
+thread_local std::string g_probe_error;
+}
+void set_error(const std::string& msg) { g_probe_error = msg; }
+int fail(int code, const std::string& msg) {
+  g_probe_error = msg;
+  return code;
+}
+}  // namespace at
+extern "C" const char* at_probe_last_error(void) { return at::g_probe_error.c_str(); }
 
 namespace at {
 

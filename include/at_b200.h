@@ -214,28 +214,6 @@ int at_engine_action_dim(const at_engine* e);
  * Lets the parity tests localise an error to the tensor-core kernels. */
 int at_engine_bf16_trunk(at_engine* e, const void* d_states, int64_t batch, float* d_trunk, void* stream);
 
-/* ---- bring-up probe ------------------------------------------------------ */
-
-/* One 128xN tcgen05.mma chain over K (bf16, fp32 accumulate in TMEM) on operand
- * images the caller laid out, with the descriptor fields given explicitly.
- * Test-only: pins the shared-memory descriptor conventions the tower relies on. */
-int at_probe_umma(const void* d_a_image, int64_t a_bytes, const void* d_b_image, int64_t b_bytes, int n, int k,
-                  uint32_t a_start_off, uint32_t a_lbo, uint32_t a_sbo, uint32_t a_kstep, uint32_t b_start_off, uint32_t b_lbo,
-                  uint32_t b_sbo, uint32_t b_kstep, int layout_type, float* d_out /* [128,n] */, uint32_t* d_status, void* stream);
-
-/* Same chain with the A operand in tensor memory (rows = TMEM lanes, two bf16 per 32-bit column, written with
- * tcgen05.st from row-major bf16 bit patterns [128,k]). Test-only: pins the layout the attention P*V product uses. */
-int at_probe_umma_ts(const void* d_a_rows, const void* d_b_image, int64_t b_bytes, int n, int k, int pack_mode, uint32_t a_col,
-                     uint32_t a_cols_per_kstep, uint32_t b_start_off, uint32_t b_lbo, uint32_t b_sbo, uint32_t b_kstep, float* d_out,
-                     uint32_t* d_status, void* stream);
-
-/* Throughput probe: every CTA of `grid` issues `mmas` back-to-back 128 x n x 16 bf16 MMAs (operands in shared memory, the
- * tower's layout) from `issuers` (1 or 2) warps, optionally while another warp streams 16 KB bulk copies into shared
- * memory (`copy` != 0) and `epi_warps` warps read tensor memory / store to shared memory like the tower's epilogue.
- * d_cycles[cta] = SM cycles per MMA of issuer 0. No reference counterpart: measures the hardware ceiling DESIGN.md quotes. */
-int at_probe_mma_rate(int n, int mmas, int issuers, int copy, int epi_warps, const void* d_src /* >= 32 KB */, int grid,
-                      float* d_cycles /* [grid] */, void* stream);
-
 #ifdef __cplusplus
 }
 #endif

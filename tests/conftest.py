@@ -22,7 +22,8 @@ def pytest_sessionstart(session):
     import shutil
     import subprocess
 
-    wanted = [ROOT / "alphatriangle_b200" / "libat_b200.so", ROOT / "alphatriangle_b200" / "_pyhost.so", ROOT / "oracle" / "liboracle_features.so"]
+    wanted = [ROOT / "alphatriangle_b200" / "libat_b200.so", ROOT / "alphatriangle_b200" / "libat_b200_probe.so",
+              ROOT / "alphatriangle_b200" / "_pyhost.so", ROOT / "oracle" / "liboracle_features.so"]
     if all(w.exists() for w in wanted) or not shutil.which("make"):
         return
     jobs = str(min(8, os.cpu_count() or 1))

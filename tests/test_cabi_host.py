@@ -19,6 +19,13 @@ def test_library_exports_every_declared_symbol():
     header = (ROOT / "include" / "at_b200.h").read_text()
     declared = set(re.findall(r"\b(at_[a-z0-9_]+)\s*\(", header))
     assert declared == set(_lib.EXPORTS), declared ^ set(_lib.EXPORTS)
+    # the bring-up probes have their own header and library
+    probe_header = (ROOT / "include" / "at_b200_probe.h").read_text()
+    probe_declared = set(re.findall(r"\b(at_probe_[a-z0-9_]+)\s*\(", probe_header))
+    assert probe_declared == set(_lib.PROBE_EXPORTS), probe_declared ^ set(_lib.PROBE_EXPORTS)
+    probe = _lib.load_probe()
+    assert all(hasattr(probe, name) for name in _lib.PROBE_EXPORTS)
+    assert not any(name.startswith("at_probe") for name in _lib.EXPORTS)
     lib = C.CDLL(str(_lib.LIB_PATH))
     for name in declared:
         assert hasattr(lib, name), f"{name} not exported"

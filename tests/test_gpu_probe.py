@@ -39,7 +39,7 @@ def test_mma_rate_probe_reports_the_pipe_rate():
 
     from alphatriangle_b200 import _lib
 
-    lib = _lib.load()
+    lib = _lib.load_probe()
     src = torch.zeros(1 << 16, dtype=torch.uint8, device="cuda")
     out = torch.zeros(8, dtype=torch.float32, device="cuda")
     assert lib.at_probe_mma_rate(128, 1024, 2, 0, 0, src.data_ptr(), 8, out.data_ptr(), None) == 0

@@ -12,7 +12,7 @@ import torch
 sys.path.insert(0, str(Path(__file__).resolve().parents[1]))
 from alphatriangle_b200 import _lib  # noqa: E402
 
-lib = _lib.load()
+lib = _lib.load_probe()
 src = torch.zeros(1 << 16, dtype=torch.uint8, device="cuda")
 grid = 148
 out = torch.zeros(grid, dtype=torch.float32, device="cuda")

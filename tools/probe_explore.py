@@ -39,7 +39,7 @@ def image_sw128(mat: np.ndarray) -> np.ndarray:
 
 
 def run(a_img, b_img, n, k, a, b, layout):
-    lib = _lib.load()
+    lib = _lib.load_probe()
     dev = torch.device("cuda")
     da = torch.from_numpy(a_img.view(np.uint8).reshape(-1).copy()).to(dev)
     db = torch.from_numpy(b_img.view(np.uint8).reshape(-1).copy()).to(dev)
@@ -50,7 +50,7 @@ def run(a_img, b_img, n, k, a, b, layout):
         a["start"], a["lbo"], a["sbo"], a["kstep"], b["start"], b["lbo"], b["sbo"], b["kstep"], layout,
         C.c_void_p(out.data_ptr()), C.c_void_p(status.data_ptr()), None,
     )
-    _lib.check(rc, "at_probe_umma")
+    _lib.check_probe(rc, "at_probe_umma")
     torch.cuda.synchronize()
     return out.cpu().numpy(), int(status.item())
 

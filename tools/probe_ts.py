@@ -14,7 +14,7 @@ from alphatriangle_b200 import _lib  # noqa: E402
 
 
 def run_ts(A, B, pack_mode, a_col, cols_per_kstep):
-    lib = _lib.load()
+    lib = _lib.load_probe()
     dev = torch.device("cuda")
     n, k = B.shape
     da = torch.from_numpy(bf16_bits(A).astype(np.int16)).to(dev)
@@ -24,7 +24,7 @@ def run_ts(A, B, pack_mode, a_col, cols_per_kstep):
     status = torch.zeros(1, dtype=torch.int32, device=dev)
     rc = lib.at_probe_umma_ts(C.c_void_p(da.data_ptr()), C.c_void_p(db.data_ptr()), db.numel(), n, k, pack_mode, a_col, cols_per_kstep,
                               0, n * 16, 128, 2 * n * 16, C.c_void_p(out.data_ptr()), C.c_void_p(status.data_ptr()), None)
-    _lib.check(rc, "at_probe_umma_ts")
+    _lib.check_probe(rc, "at_probe_umma_ts")
     torch.cuda.synchronize()
     return out.cpu().numpy(), int(status.item())
 
