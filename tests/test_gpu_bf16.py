@@ -194,3 +194,33 @@ def test_other_head_kernels_match_oracle(shape, fmt):
     assert kl.max() <= KL_TOL
     assert verr.max() <= 0.3
     assert np.abs(probs.cpu().numpy().sum(axis=1) - 1.0).max() < 1e-5
+
+
+ENCODER_SHAPES = {
+    "one_layer_ff128_gelu": dict(TRANSFORMER_LAYERS=1, TRANSFORMER_FC_DIM=128, ACTIVATION_FUNCTION="GELU"),  # a single hidden half
+    "three_layers_ff512": dict(TRANSFORMER_LAYERS=3, TRANSFORMER_FC_DIM=512),                               # four hidden halves
+    "four_layers_ff384": dict(TRANSFORMER_LAYERS=4, TRANSFORMER_FC_DIM=384),
+}
+
+
+@pytest.mark.parametrize("fmt", FORMATS)
+@pytest.mark.parametrize("shape", sorted(ENCODER_SHAPES))
+def test_other_encoder_shapes_match_oracle(shape, fmt):
+    """The fused tower + encoder kernel outside the default 2 layers x 256: the weight ring's slab order (projection, bias
+    and LayerNorm folds, hidden halves) is generated per shape on the host and must match what the issuers consume."""
+    import alphatriangle_b200 as at
+    from alphatriangle_b200.synth import synth_state_dict
+
+    mc, env = at.ModelConfig(**ENCODER_SHAPES[shape]), at.EnvConfig()
+    nn = at.NeuralNetwork(mc, env, None, torch.device("cuda:0"), precision=fmt, max_batch=256)
+    assert nn.precision in _lib.TENSOR_CORE_PRECISIONS
+    nn.set_weights(synth_state_dict(nn.get_weights(), 91, sharpness=1.0))
+    states = synth_states(101, env, seed=777) + edge_states(env)
+    grid, other = features_ref.extract_batch(states, mc)
+    p_ref, v_ref = model_ref.evaluate_tensors(nn.get_weights(), mc, grid, other)
+    probs, value = nn.evaluate_packed(torch.from_numpy(pack_states(states, env)).cuda())
+    kl = kl_rows(p_ref, probs.cpu().numpy())
+    verr = np.abs(value.cpu().numpy() - v_ref)
+    print(f"[{fmt} parity] {shape}: policy KL max {kl.max():.3e}; value |err| max {verr.max():.3e}")
+    assert kl.max() <= KL_TOL
+    assert verr.max() <= 0.3
