@@ -85,6 +85,9 @@ class NeuralNetwork:
         if precision == "auto":
             if not self.engine.supports(_lib.PREC_BF16):
                 self.precision = _lib.PREC_FP32
+                # not silent: this configuration runs 20-30x slower than one the tcgen05 kernels cover
+                logger.warning("precision='auto': this ModelConfig is outside the tcgen05 path (%s); using the fp32 CUDA-core path",
+                               _lib.last_error())
             else:
                 self.precision = _lib.PREC_F16 if model_config.USE_BATCH_NORM else _lib.PREC_BF16
         elif precision in _PRECISIONS:
