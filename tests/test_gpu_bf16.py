@@ -224,3 +224,31 @@ def test_other_encoder_shapes_match_oracle(shape, fmt):
     print(f"[{fmt} parity] {shape}: policy KL max {kl.max():.3e}; value |err| max {verr.max():.3e}")
     assert kl.max() <= KL_TOL
     assert verr.max() <= 0.3
+
+
+@pytest.mark.parametrize("fmt", FORMATS)
+@pytest.mark.parametrize("case", BF16_CASES)
+def test_repeated_evaluations_are_bit_identical(case, fmt, golden_dir):
+    """The pipelines inside the tower kernels hand shared-memory images, accumulators and ring stages from warp to warp and
+    from one board pair to the next; a missing fence or barrier shows up as run-to-run differences long before it shows up
+    as a wrong answer. 40 launches at a batch that gives every CTA a different number of pairs must agree bit for bit."""
+    mc, env, _seed, g = load_case(case, golden_dir)
+    nn = network(case, fmt)
+    base = g["packed"]
+    n = 4096 + 37
+    packed = torch.from_numpy(np.tile(base, (-(-n // base.shape[0]), 1))[:n]).cuda()
+    big = at_network_for(nn, n)
+    p0, v0 = [t.clone() for t in big.evaluate_packed(packed)]
+    for _ in range(40):
+        p, v = big.evaluate_packed(packed)
+        assert torch.equal(p, p0) and torch.equal(v, v0)
+
+
+def at_network_for(nn, batch):
+    """A network with the same weights and precision whose engine holds `batch` states."""
+    import alphatriangle_b200 as at
+
+    name = _lib.PRECISION_NAMES[nn.precision]
+    big = at.NeuralNetwork(nn.model_config, nn.env_config, None, nn.device, precision=name, max_batch=batch)
+    big.set_weights(nn.get_weights())
+    return big
