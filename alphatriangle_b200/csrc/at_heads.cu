@@ -461,14 +461,14 @@ __global__ void __launch_bounds__(kMmaThreads, 1) heads_mma_kernel(const HeadsPa
       if (b < n_here) {
         v = __ldg(reinterpret_cast<const float4*>(p.trunk_bias + n));
         const float4* pp = reinterpret_cast<const float4*>(p.partial) + (size_t)(b0 + b) * K4 + (n >> 2);
-#pragma unroll 4
-        for (int z = 0; z < p.splits; ++z) {
+#pragma unroll 8
+        for (int z = 0; z < p.splits; ++z) {  // independent L2 loads: keep many in flight
           const float4 q = __ldg(pp + z * split_stride);
           v.x += q.x; v.y += q.y; v.z += q.z; v.w += q.w;
         }
         const float4* wo = reinterpret_cast<const float4*>(p.w_other + n);
         const float* ob = o_s + b * p.other_dim;
-#pragma unroll 2
+#pragma unroll 10
         for (int k = 0; k < p.other_dim; ++k) {
           const float4 w = __ldg(wo + (size_t)k * K4);
           const float o = ob[k];
