@@ -157,7 +157,7 @@ int at_engine_evaluate_packed(at_engine* e, int precision, const void* d_states,
                               uint32_t* d_flags, void* stream);
 
 /* No counterpart in the reference. at_engine_evaluate_packed for up to 128 states (four default MCTS leaf
- * batches) on the bf16 path, for hosts that must not allocate device memory once they are running:
+ * batches) on the tensor-core path (in the operand format the engine served last: bf16 until an fp16 evaluation was made), for hosts that must not allocate device memory once they are running:
  *   - a self-play process that shares its GPU with the trainer, where a cudaMalloc / cudaFree in the search loop
  *     would synchronise the whole device and stall the trainer's streams, or fail once the trainer has taken the rest
  *     of the memory;
@@ -174,7 +174,7 @@ int at_engine_evaluate_packed(at_engine* e, int precision, const void* d_states,
  *   - Every engine and every call on a GPU share the array and it keeps the previous call's bytes. Nothing in it needs
  *     clearing (each call rewrites all rows it later reads), but two calls whose kernels overlap on the GPU -- different
  *     streams, threads or engines -- race on it: serialise them (one stream, or events).
- *   - Needs the bf16 path and the fused-head shape (one shared FC layer, one hidden layer per head). */
+ *   - Needs the tensor-core path and the fused-head shape (one shared FC layer, one hidden layer per head). */
 int at_engine_evaluate_packed_static(at_engine* e, const void* d_states, int64_t batch, float* d_policy, float* d_value,
                                      uint32_t* d_flags, void* stream);
 

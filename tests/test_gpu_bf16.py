@@ -252,3 +252,33 @@ def at_network_for(nn, batch):
     big = at.NeuralNetwork(nn.model_config, nn.env_config, None, nn.device, precision=name, max_batch=batch)
     big.set_weights(nn.get_weights())
     return big
+
+
+def test_fp16_operands_saturate_instead_of_overflowing():
+    """fp16's range ends at 65504. A network whose activations go beyond it (here: the first convolution scaled by 3e5) must
+    not produce infinities or NaNs on the fp16 path -- the conversions clamp -- and the bf16 path, whose range is fp32's,
+    must still track the reference. That is the trade-off precision="auto" decides by."""
+    import alphatriangle_b200 as at
+    from alphatriangle_b200.synth import synth_state_dict
+
+    mc, env = at.ModelConfig(USE_TRANSFORMER=False), at.EnvConfig()
+    states = synth_states(64, env, seed=31)
+    packed = torch.from_numpy(pack_states(states, env)).cuda()
+    sd = None
+    out = {}
+    for fmt in FORMATS:
+        nn = at.NeuralNetwork(mc, env, None, torch.device("cuda:0"), precision=fmt, max_batch=64)
+        if sd is None:
+            sd = synth_state_dict(nn.get_weights(), 5, sharpness=1.0)
+            sd["conv_body.0.0.weight"] = sd["conv_body.0.0.weight"] * 3e5  # BatchNorm follows, but its input is the conv output
+            sd["conv_body.0.1.running_var"] = sd["conv_body.0.1.running_var"] * 0 + 1.0
+            sd["conv_body.0.1.weight"] = sd["conv_body.0.1.weight"] * 0 + 1.0
+        nn.set_weights(sd)
+        probs, value, flags = nn.engine.evaluate_packed(packed, nn.precision)
+        assert int(flags[0].item()) == 0
+        assert bool(torch.isfinite(probs).all()) and bool(torch.isfinite(value).all())
+        assert np.abs(probs.cpu().numpy().sum(axis=1) - 1.0).max() < 1e-5
+        out[fmt] = probs.cpu().numpy()
+    grid, other = features_ref.extract_batch(states, mc)
+    p_ref, _v = model_ref.evaluate_tensors(sd, mc, grid, other)
+    assert (out["bf16"].argmax(axis=1) == p_ref.argmax(axis=1)).mean() >= 0.9  # bf16 follows the reference through 1e5-sized activations
