@@ -19,11 +19,29 @@ flush = int(sys.argv[3]) if len(sys.argv) > 3 else 0
 golden = ROOT / "tests" / "golden"
 junk = torch.empty(512 << 20, dtype=torch.uint8, device="cuda") if flush else None
 
-for case in ("default_tf", "conv_only"):
+import alphatriangle_b200 as at  # noqa: E402
+from alphatriangle_b200.packing import pack_states  # noqa: E402
+from alphatriangle_b200.synth import synth_state_dict, synth_states  # noqa: E402
+
+SHAPES = {  # model shapes beyond the golden cases (same ones tests/test_gpu_bf16.py checks against the oracle)
+    "tf_1layer_ff128_gelu": dict(TRANSFORMER_LAYERS=1, TRANSFORMER_FC_DIM=128, ACTIVATION_FUNCTION="GELU"),
+    "tf_3layers_ff512": dict(TRANSFORMER_LAYERS=3, TRANSFORMER_FC_DIM=512),
+    "tf_cuda_core_heads": dict(FC_DIMS_SHARED=[96], POLICY_HEAD_DIMS=[48], VALUE_HEAD_DIMS=[24]),
+    "conv_unfused_tail": dict(USE_TRANSFORMER=False, FC_DIMS_SHARED=[128, 64], POLICY_HEAD_DIMS=[64, 32], VALUE_HEAD_DIMS=[]),
+}
+cases = sys.argv[4].split(",") if len(sys.argv) > 4 else ["default_tf", "conv_only"]
+
+for case in cases:
     for fmt in ("f16", "bf16"):
-        _mc, _env, _seed, g = load_case(case, golden)
-        nn = network(case, fmt, max_batch=max(batch, 4096))
-        base = g["packed"]
+        if case in SHAPES:
+            mc, env = at.ModelConfig(**SHAPES[case]), at.EnvConfig()
+            nn = at.NeuralNetwork(mc, env, None, torch.device("cuda:0"), precision=fmt, max_batch=max(batch, 4096))
+            nn.set_weights(synth_state_dict(nn.get_weights(), 91, sharpness=1.0))
+            base = pack_states(synth_states(48, env, seed=777), env)
+        else:
+            _mc, _env, _seed, g = load_case(case, golden)
+            nn = network(case, fmt, max_batch=max(batch, 4096))
+            base = g["packed"]
         n = base.shape[0]
         packed = torch.from_numpy(np.tile(base, (-(-batch // n), 1))[:batch]).cuda()
         idx = torch.arange(batch, device="cuda") % n
