@@ -124,6 +124,9 @@ __host__ __device__ constexpr uint32_t idesc_16(uint32_t m, uint32_t n, uint32_t
          | ((m >> 4) << 24);  // M / 16
 }
 __host__ __device__ constexpr uint32_t idesc_bf16(uint32_t m, uint32_t n) { return idesc_16(m, n, 1u); }
+// Same, B taken MN-major: the shared-memory image holds, for every key (K index), its N values contiguously -- [N / 8][K][8]
+// with no swizzle, i.e. descriptor LBO = stride between groups of 8 K rows (128 B), SBO = stride between groups of 8 N values.
+__host__ __device__ constexpr uint32_t idesc_16_b_mn(uint32_t m, uint32_t n, uint32_t bf16) { return idesc_16(m, n, bf16) | (1u << 16); }
 
 // D[tmem] (+)= A[smem] * B[smem]^T ; issued by ONE thread on behalf of the CTA
 __device__ __forceinline__ void mma_bf16(uint32_t tmem_d, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, bool accumulate) {
@@ -158,6 +161,15 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
         "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]), "=r"(r[17]), "=r"(r[18]),
         "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]),
         "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]), "=r"(r[9]),
+        "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
       : "r"(taddr)
       : "memory");
 }
