@@ -744,7 +744,7 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
     return AT_OK;
   };
   if (p.transformer) {
-    if (p.has_input_proj || d.t_dim != kTfD || p.cnn_ch != kTfD) return no("transformer on the tcgen05 path needs TRANSFORMER_DIM = last conv channels = 128");
+    if (d.t_dim != kTfD) return no("transformer on the tcgen05 path needs TRANSFORMER_DIM = 128");
     if (d.t_heads * kTfDh != kTfD) return no("transformer on the tcgen05 path needs head width 32");
     if (d.t_ff % 128 != 0 || d.t_ff > 1024) return no("TRANSFORMER_FC_DIM must be a multiple of 128, at most 1024");
     if (d.t_layers > kMaxTfLayers) return no("at most 4 transformer layers on the tcgen05 path");
@@ -759,6 +759,15 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
   for (const ResBlock& r : p.res) {
     seq.push_back(&r.c1);
     seq.push_back(&r.c2);
+  }
+  // input_proj (model.py:179-186: a 1x1 convolution to TRANSFORMER_DIM when the tower ends on another width, no activation)
+  // is one more tensor-core layer whose output becomes the residual stream
+  ConvLayer proj;
+  const bool with_proj = p.transformer && p.has_input_proj;
+  if (with_proj) {
+    proj.f = p.input_proj;
+    proj.cin = p.cnn_ch; proj.cout = d.t_dim; proj.kh = proj.kw = 1;
+    seq.push_back(&proj);
   }
   if ((int)seq.size() - 1 > kMaxLayers || seq.size() < 2) return no("needs 2..13 convolution layers");
   for (size_t i = 0; i < seq.size(); ++i) {
@@ -821,7 +830,8 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
     add(p.res[r].c1, cur, cur ^ 1, -1);
     add(p.res[r].c2, cur ^ 1, cur, cur);
   }
-  if (n_plain == 1 && p.res.empty()) {
+  if (with_proj) add(proj, cur, cur ^ 1, -1);
+  if (n_plain == 1 && p.res.empty() && !with_proj) {
     delete b;
     return no("needs a tensor-core layer after the first convolution");
   }

@@ -223,6 +223,11 @@ ENCODER_SHAPES = {
     "one_layer_ff128_gelu": dict(TRANSFORMER_LAYERS=1, TRANSFORMER_FC_DIM=128, ACTIVATION_FUNCTION="GELU"),  # a single hidden half
     "three_layers_ff512": dict(TRANSFORMER_LAYERS=3, TRANSFORMER_FC_DIM=512),                               # four hidden halves
     "four_layers_ff384": dict(TRANSFORMER_LAYERS=4, TRANSFORMER_FC_DIM=384),
+    # tower ends on 64 channels: 1x1 projection into the residual blocks and input_proj (model.py:179-186) up to the
+    # encoder's 128 -- both 1x1 layers run on the tensor cores, input_proj without activation
+    "input_proj_from_64": dict(RESIDUAL_BLOCK_FILTERS=64, NUM_RESIDUAL_BLOCKS=1),
+    "input_proj_from_32_no_res": dict(CONV_FILTERS=[32, 32], CONV_KERNEL_SIZES=[3, 3], CONV_STRIDES=[1, 1], CONV_PADDING=[1, 1],
+                                      NUM_RESIDUAL_BLOCKS=0, TRANSFORMER_LAYERS=1),
 }
 
 
