@@ -74,7 +74,7 @@ constexpr long long kTimeoutCycles = 2000000000LL;  // ~1 s: a wedged pipeline r
 #define AT_DBG(bits) ((p.debug & (bits)) != 0)
 // Timeline of one board pair in CTA 0 (experiments build only): every warp's lane 0 stamps clock64() at named points into
 // g_timeline[warp][event]; tools/tower_timeline.py prints them relative to the pair's start (at_debug_read_timeline).
-constexpr int kTlEvents = 96;
+constexpr int kTlEvents = 256;
 __device__ unsigned long long g_timeline[32 * kTlEvents];
 #define AT_TL_DECL int tl_i = 0; bool tl_on = false;
 #define AT_TL_PAIR(pair) tl_on = (blockIdx.x == 0 && (pair) == (int64_t)3 * gridDim.x); tl_i = 0;
@@ -693,7 +693,7 @@ __global__ void __launch_bounds__(kFcThreads, 2) fc_kernel(const __grid_constant
 
 constexpr size_t tower_tf_smem_bytes() {
   return (size_t)kTfStages * kStageBytes + (size_t)kBoards * 2 * kBufBytes + kMaskBytes + (size_t)kMaxLayers * 128 * 4 + 9 * 128 * 4 +
-         128 * 4 + (size_t)kXchFloats * 4 + (2 * kStages + 8) * 8 + 16;
+         128 * 4 + (size_t)kXchFloats * 4 + (size_t)kTfBars * 8 + 16;
 }
 
 }  // namespace
@@ -860,31 +860,28 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
       if (n < kMaxRingSlabs) t.slab16[n] = (uint16_t)(bytes / 16);
       ++n;
     };
-    auto bias_slab = [&](int N) { slab(2u * (uint32_t)N * 16u); };  // two 8-wide K planes, row 0 = the bias
     for (int l = 0; l < tp.n_layers; ++l)
       for (int sl = 0; sl < tp.layers[l].n_slabs; ++sl) slab(tp.layers[l].slab_bytes);
+    t.n_conv_slabs = n;
+    // An encoder GEMM goes through the ring in slabs of `steps` K-steps of 16 rows, its bias planes (two 8-wide K planes, row 0 =
+    // the bias) as one more slab. The operand images are the same bytes whatever the cut: K planes back to back, the bias planes
+    // right behind them (bf16_add_prep_jobs writes them in this order). No slab may exceed a 12 KB encoder stage.
+    auto gemm_slabs = [&](int N, int K, int steps, bool bias) {
+      for (int k0 = 0; k0 < K; k0 += steps * 16) slab((uint32_t)N * (K - k0 < steps * 16 ? K - k0 : steps * 16) * 2);
+      if (bias) slab(2u * N * 16u);
+    };
     // the encoder's slabs in the order the issuers consume them (tower_tf_kernel, "encoder layers")
     for (int l = 0; l < d.t_layers; ++l) {
-      auto qkv_slabs = [&]() {
-        slab(3 * kTfDh * 64 * 2); slab(3 * kTfDh * 64 * 2);   // fused q|k|v projection of one head, two K halves
-        bias_slab(3 * kTfDh);
-      };
-      qkv_slabs();                                            // head 0
+      gemm_slabs(3 * kTfDh, kTfD, kQkvSteps, true);                         // fused q|k|v projection of head 0
       for (int h = 0; h < d.t_heads; ++h) {
-        if (h + 1 < d.t_heads) qkv_slabs();                   // head h+1's projection is issued right behind head h's P V
-        slab(kTfD * kTfDh * 2);                               // out_proj columns of head h
-        if (h == 0) bias_slab(kTfD);                          // out_proj bias
+        if (h + 1 < d.t_heads) gemm_slabs(3 * kTfDh, kTfD, kQkvSteps, true);  // head h+1's projection is issued right behind head h's P V
+        gemm_slabs(kTfD, kTfDh, 2, h + 1 == d.t_heads);                     // out_proj columns of head h; its bias behind the last head
       }
       for (int f = 0; f < t.ff_halves; ++f) {
-        if (f > 0) {
-          slab(128 * 64 * 2); slab(128 * 64 * 2);             // linear2, hidden half f-1
-          if (f == 1) bias_slab(kTfD);                        // linear2 bias
-        }
-        slab(128 * 64 * 2); slab(128 * 64 * 2);               // linear1, hidden half f
-        bias_slab(128);
+        if (f > 0) gemm_slabs(kTfD, 128, kFfnSteps, f == 1);                // linear2, hidden half f-1 (+ its bias, once)
+        gemm_slabs(128, kTfD, kFfnSteps, true);                             // linear1, hidden half f
       }
-      slab(128 * 64 * 2); slab(128 * 64 * 2);
-      if (t.ff_halves == 1) bias_slab(kTfD);
+      gemm_slabs(kTfD, 128, kFfnSteps, t.ff_halves == 1);
     }
     b->wstream_bytes = 0;
     for (int i = 0; i < n && i < kMaxRingSlabs; ++i) b->wstream_bytes += (size_t)t.slab16[i] * 16;
@@ -1048,7 +1045,7 @@ void bf16_add_prep_jobs(const Bf16Path* b, const Plan& p, PrepList& list) {
     for (int h = 0; h < d.t_heads; ++h) {
       if (h + 1 < d.t_heads) qkv_proj(h + 1);
       out_proj(h);
-      if (h == 0) bias(e.out.bias, -1, -1, out_all);
+      if (h + 1 == d.t_heads) bias(e.out.bias, -1, -1, out_all);
     }
     auto linear2 = [&](int f) { pack(e.ff2.wt, Sel{kTfD, 128, f * 128, kTfD, kTfD, {0, 0, 0}, 1.0f}, -1); };
     for (int f = 0; f < halves; ++f) {

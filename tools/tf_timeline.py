@@ -30,7 +30,7 @@ for _ in range(3):
     nn.engine.evaluate_packed(packed, nn.precision)
 torch.cuda.synchronize()
 lib = _lib.load()
-EV = 96
+EV = 256
 buf = (C.c_uint64 * (32 * EV))()
 lib.at_debug_read_timeline.restype = C.c_int
 lib.at_debug_read_timeline.argtypes = [C.c_void_p, C.c_int]
@@ -61,9 +61,13 @@ for i, c in enumerate(commit):
     if i >= len(acc[2]):
         break
     a2 = acc[2][i]
-    p2 = post[2][i + 1] if i + 1 < len(post[2]) else -1   # post 0 is the pair's layer-0 image (before any accumulator)
-    p6 = post[6][i + 1] if i + 1 < len(post[6]) else -1
+    # the pair's layer-0 image was posted during the previous pair (not stamped): post i answers accumulator i
+    p2 = post[2][i] if i < len(post[2]) else -1
+    p6 = post[6][i] if i < len(post[6]) else -1
     name = labels[i] if i < len(labels) else "?"
     print(f"{name:12s} {c:7d} {a2:8d} {p2:10d} {p6:10d} | {a2 - c:10d} {max(p2, p6) - a2:8d}")
+# issuer A in full: tag:cycle (3 operands seen, 5 weight slab seen, 4 issued + committed)
+w = 1
+print("issuer A all:", " ".join(f"{int(tags[w, i])}:{int(clk[w, i] - t0)}" for i in range(EV) if tags[w, i] > 0))
 print("issuer waits (operands seen):", " ".join(str(x) for x in seen))
 print("total cycles for the pair:", max(max(v) for v in post.values() if v) - min(seen))

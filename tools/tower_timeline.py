@@ -30,7 +30,7 @@ for _ in range(3):
     nn.engine.evaluate_packed(packed, nn.precision)
 torch.cuda.synchronize()
 lib = _lib.load()
-EV = 96
+EV = 256
 buf = (C.c_uint64 * (32 * EV))()
 lib.at_debug_read_timeline.restype = C.c_int
 lib.at_debug_read_timeline.argtypes = [C.c_void_p, C.c_int]
