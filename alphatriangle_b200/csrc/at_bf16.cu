@@ -732,7 +732,7 @@ struct Bf16Path {
   TowerTfParams ttp{};
   float* fc_bias[2] = {nullptr, nullptr};  // trunk FC bias with the encoder's final LayerNorm folded in (fp32 [fc_n])
   int64_t fc_bias_off = 0;                  // the plain bias in the folded set
-  size_t conv_stream_bytes = 0;
+  size_t conv_stream_bytes = 0, pe_t_off = 0;
   int packed_fmt[2] = {-1, -1};             // operand format the 16-bit images of each weight set currently hold
 };
 
@@ -885,6 +885,8 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
     }
     b->wstream_bytes = 0;
     for (int i = 0; i < n && i < kMaxRingSlabs; ++i) b->wstream_bytes += (size_t)t.slab16[i] * 16;
+    b->pe_t_off = b->wstream_bytes;  // behind the slabs: the positional table, transposed for coalesced loads (PK_PE_T)
+    b->wstream_bytes += (size_t)p.L * kTfD * sizeof(float);
     b->fc_bias_off = fc.bias;
     t.n_ring_slabs = n;
     if (n > kMaxRingSlabs) {
@@ -1062,6 +1064,11 @@ void bf16_add_prep_jobs(const Bf16Path* b, const Plan& p, PrepList& list) {
     // this layer's norm1 belongs to its own q|k|v projection (handled above); the NEXT layer's norm1, or the encoder's
     // final norm, is applied to this layer's output and folded into whatever consumes it
   }
+  PrepJob j{};
+  j.kind = PK_PE_T; j.phase = 1;
+  j.a[0] = p.pe; j.a[1] = (int64_t)b->pe_t_off;
+  j.i[0] = p.L; j.i[1] = kTfD;
+  list.add(j, (int64_t)p.L * kTfD);
 }
 
 int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slot, const void* d_states, int64_t batch, int* n_splits,
@@ -1096,7 +1103,8 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
   if (b->tf) {
     TowerTfParams t = b->ttp;
     t.conv = tp;
-    t.pe = folded + p.pe;
+    t.pe = reinterpret_cast<const float*>(b->wstream[slot] + b->pe_t_off);
+    t.n_pos = p.L;
 #define AT_TF_LAUNCH(ACT_)                                                                                          \
   do {                                                                                                              \
     if (fmt == FMT_F16) tower_tf_kernel<ACT_, FMT_F16><<<grid, kTfThreads, tower_tf_smem_bytes(), st>>>(t);          \

@@ -153,6 +153,19 @@ __device__ void job_bias_slab(const PrepJob& j, const PrepBases& b, int fmt, int
   }
 }
 
+// PK_PE_T   positional table [P][D] fp32 (folded + a0) -> [D / 4][P][4] fp32 at BYTE offset a1 of the weight stream: the fused
+// kernel's threads are one per position, so a warp's 16-byte loads of one column group are then 512 contiguous bytes
+// instead of 32 different cache lines.  i: P, D
+__device__ void job_pe_t(const PrepJob& j, const PrepBases& b, int rank, int nb) {
+  const float* __restrict__ src = static_cast<const float*>(b.p[PB_FOLDED]) + j.a[0];
+  float* __restrict__ dst = reinterpret_cast<float*>(static_cast<unsigned char*>(b.p[PB_WSTREAM]) + j.a[1]);
+  const int P = j.i[0], D = j.i[1];
+  for (int i = rank * blockDim.x + threadIdx.x; i < P * D; i += nb * blockDim.x) {
+    const int cg = i / (P * 4), rem = i - cg * P * 4;
+    dst[i] = src[(rem >> 2) * D + cg * 4 + (rem & 3)];
+  }
+}
+
 // PK_FC_BIAS   trunk FC bias with the encoder's final LayerNorm folded in: out[n] = bias[n] + sum_k Wt[k][n] * beta[k % period]
 // a: bias, Wt, beta (folded floats)   i: K, N, period.   One block; thread (n, part) sums a K range, parts combined in shared memory.
 __device__ void job_fc_bias(const PrepJob& j, const PrepBases& b, int rank, int nb) {
@@ -227,6 +240,7 @@ __global__ void __launch_bounds__(256) prep_kernel(const PrepJob* __restrict__ j
     case PK_PACK_FRAG: job_pack_frag(job, bases, fmt, rank, nb); break;
     case PK_BIAS_SLAB: job_bias_slab(job, bases, fmt, rank, nb); break;
     case PK_FC_BIAS: job_fc_bias(job, bases, rank, nb); break;
+    case PK_PE_T: job_pe_t(job, bases, rank, nb); break;
     default: break;
   }
 }

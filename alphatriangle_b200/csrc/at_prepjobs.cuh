@@ -14,7 +14,7 @@
 namespace at {
 
 enum PrepBase : int { PB_IMAGE = 0, PB_FOLDED, PB_WSTREAM, PB_WFC, PB_BIAS, PB_FCBIAS, PB_FRAGS, PB_COUNT };
-enum PrepKind : int { PK_FOLD = 0, PK_COPY, PK_PACK_B, PK_PACK_SEL, PK_GATHER_BIAS, PK_PACK_FRAG, PK_BIAS_SLAB, PK_FC_BIAS };
+enum PrepKind : int { PK_FOLD = 0, PK_COPY, PK_PACK_B, PK_PACK_SEL, PK_GATHER_BIAS, PK_PACK_FRAG, PK_BIAS_SLAB, PK_FC_BIAS, PK_PE_T };
 
 struct PrepJob {
   int kind, phase, first_block, n_blocks;

@@ -69,5 +69,7 @@ for i, c in enumerate(commit):
 # issuer A in full: tag:cycle (3 operands seen, 5 weight slab seen, 4 issued + committed)
 w = 1
 print("issuer A all:", " ".join(f"{int(tags[w, i])}:{int(clk[w, i] - t0)}" for i in range(EV) if tags[w, i] > 0))
+for w in (2, 6):
+    print(f"epilogue warp {w} all:", " ".join(f"{int(tags[w, i])}:{int(clk[w, i] - t0)}" for i in range(EV) if tags[w, i] > 0)[:700])
 print("issuer waits (operands seen):", " ".join(str(x) for x in seen))
 print("total cycles for the pair:", max(max(v) for v in post.values() if v) - min(seen))
