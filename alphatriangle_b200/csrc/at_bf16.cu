@@ -863,25 +863,23 @@ int bf16_create(const Plan& p, int64_t max_batch, Bf16Path** out, std::string* r
     for (int l = 0; l < tp.n_layers; ++l)
       for (int sl = 0; sl < tp.layers[l].n_slabs; ++sl) slab(tp.layers[l].slab_bytes);
     t.n_conv_slabs = n;
-    // An encoder GEMM goes through the ring in slabs of `steps` K-steps of 16 rows, its bias planes (two 8-wide K planes, row 0 =
-    // the bias) as one more slab. The operand images are the same bytes whatever the cut: K planes back to back, the bias planes
-    // right behind them (bf16_add_prep_jobs writes them in this order). No slab may exceed a 12 KB encoder stage.
-    auto gemm_slabs = [&](int N, int K, int steps, bool bias) {
-      for (int k0 = 0; k0 < K; k0 += steps * 16) slab((uint32_t)N * (K - k0 < steps * 16 ? K - k0 : steps * 16) * 2);
-      if (bias) slab(2u * N * 16u);
-    };
-    // the encoder's slabs in the order the issuers consume them (tower_tf_kernel, "encoder layers")
+    // The encoder's slabs in the order the issuers consume them (tower_tf_kernel: qkv_gemm, deep_gemm, ring_slab). The operand
+    // images are the same bytes whatever the cut -- K planes of 8 rows back to back, a GEMM's bias planes (two 8-wide K planes,
+    // row 0 = the bias) right behind its weights, as bf16_add_prep_jobs writes them; no slab may exceed a 12 KB encoder stage.
+    auto bias_bytes = [](int N) { return 2u * (uint32_t)N * 16u; };
+    auto qkv_slabs = [&]() { slab(3 * kTfDh * 64 * 2); slab(3 * kTfDh * 64 * 2); slab(bias_bytes(3 * kTfDh)); };
+    auto deep_slabs = [&](bool bias) { slab(128 * 48 * 2); slab(128 * 48 * 2); slab(128 * 32 * 2 + (bias ? bias_bytes(128) : 0u)); };
     for (int l = 0; l < d.t_layers; ++l) {
-      gemm_slabs(3 * kTfDh, kTfD, kQkvSteps, true);                         // fused q|k|v projection of head 0
+      qkv_slabs();                                                          // head 0
       for (int h = 0; h < d.t_heads; ++h) {
-        if (h + 1 < d.t_heads) gemm_slabs(3 * kTfDh, kTfD, kQkvSteps, true);  // head h+1's projection is issued right behind head h's P V
-        gemm_slabs(kTfD, kTfDh, 2, h + 1 == d.t_heads);                     // out_proj columns of head h; its bias behind the last head
+        if (h + 1 < d.t_heads) qkv_slabs();                                 // head h+1's projection is issued right behind head h's P V
+        slab(kTfD * kTfDh * 2 + (h + 1 == d.t_heads ? bias_bytes(kTfD) : 0u));  // out_proj columns of head h; its bias with the last head
       }
       for (int f = 0; f < t.ff_halves; ++f) {
-        if (f > 0) gemm_slabs(kTfD, 128, kFfnSteps, f == 1);                // linear2, hidden half f-1 (+ its bias, once)
-        gemm_slabs(128, kTfD, kFfnSteps, true);                             // linear1, hidden half f
+        if (f > 0) deep_slabs(f == 1);                                      // linear2, hidden half f-1 (+ its bias, once)
+        deep_slabs(true);                                                   // linear1, hidden half f
       }
-      gemm_slabs(kTfD, 128, kFfnSteps, t.ff_halves == 1);
+      deep_slabs(t.ff_halves == 1);
     }
     b->wstream_bytes = 0;
     for (int i = 0; i < n && i < kMaxRingSlabs; ++i) b->wstream_bytes += (size_t)t.slab16[i] * 16;
