@@ -64,6 +64,10 @@ constexpr int kEpiWarps = kBoards * 4 * kEpiSplit;
 constexpr int kMmaWarpB = 2 + kEpiWarps;      // MMA-issuing warp of board 1; warp 1 issues for board 0
 constexpr int kTowerThreads = 64 + kEpiWarps * 32 + 32;
 constexpr int kTowerTmemCols = AT_TOWER_OVERLAP ? 512 : kBoards * 128;  // per board one accumulator, or two used by alternate pairs
+#ifndef AT_TOWER_PAIR_DRAIN
+#define AT_TOWER_PAIR_DRAIN 1
+#endif
+constexpr bool kPairDrain = AT_TOWER_PAIR_DRAIN != 0 && AT_TOWER_OVERLAP != 0;  // last layer: 32 channels of both boards per thread
 constexpr int kMaxBars = 32;                 // mbarrier slots reserved in shared memory
 constexpr long long kTimeoutCycles = 2000000000LL;  // ~1 s: a wedged pipeline reports instead of hanging
 
@@ -214,6 +218,12 @@ __device__ __forceinline__ void add8(float (&v)[8], const uint4& w) {
   unpack2<FMT>(w.w, lo, hi); v[6] += lo; v[7] += hi;
 }
 
+// 32 bytes to global memory in one instruction (sm_100: STG.256); dst 32-byte aligned
+__device__ __forceinline__ void stg256(void* dst, const uint4& lo, const uint4& hi) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(dst), "r"(lo.x), "r"(lo.y), "r"(lo.z), "r"(lo.w),
+               "r"(hi.x), "r"(hi.y), "r"(hi.z), "r"(hi.w)
+               : "memory");
+}
 __device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
 }
@@ -281,6 +291,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   const uint32_t bar_full = smem_u32(bars), bar_empty = smem_u32(bars + NS);
   const uint32_t bar_acc0 = smem_u32(bars + 2 * NS), bar_acc1 = smem_u32(bars + 2 * NS + 1);  // accumulator of board b complete
   const uint32_t bar_act0 = smem_u32(bars + 2 * NS + 2), bar_act1 = smem_u32(bars + 2 * NS + 3);  // input image of board b written
+  const uint32_t bar_last0 = smem_u32(bars + 2 * NS + 4), bar_last1 = smem_u32(bars + 2 * NS + 5);  // a pair's last accumulator of board b
   const bool use_ring = !AT_DBG(16u);  // 16: timing experiment without the weight ring (issue loop + MMAs + epilogue only)
 
   // ---- one-time setup --------------------------------------------------------------------
@@ -297,6 +308,8 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     mbar_init(bar_acc1, 1);
     mbar_init(bar_act0, kEpiWarps / kBoards);  // one arrival per epilogue warp of the board
     mbar_init(bar_act1, kEpiWarps / kBoards);
+    mbar_init(bar_last0, 1);
+    mbar_init(bar_last1, 1);
     fence_mbar_init();
   }
   if (warp == 0) {
@@ -399,7 +412,10 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
           stage = stage + 1 == NS ? 0 : stage + 1;
           phase ^= (stage == 0);
         }
-        if (ok && elect_one()) mma_commit(my_acc);
+        if (ok && elect_one()) {
+          mma_commit(my_acc);
+          if (kPairDrain && l + 1 == p.n_layers) mma_commit(me == 0 ? bar_last0 : bar_last1);  // for the sibling board's epilogue warps
+        }
         __syncwarp();
         AT_TL(30 + l);  // last slab issued, accumulator committed
       }
@@ -417,7 +433,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     const int pos = y * p.cols + x;  // compact position index (token order h*W + w)
     const uint32_t my_act_u = act_u + (uint32_t)eb * 2 * kBufBytes + (uint32_t)(kHalo + m) * 16;  // this row, plane 0, buffer 0
     const uint32_t tmem_row0 = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)eb * 128;
-    uint32_t acc_phase = 0, par = 0;
+    uint32_t acc_phase = 0, par = 0, last_phase = 0;
     bool ok = true;
     const uint32_t my_act = eb == 1 ? bar_act1 : bar_act0;
     const uint32_t my_acc = eb == 1 ? bar_acc1 : bar_acc0;
@@ -549,9 +565,58 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
             }
           }
         };
+        // The LAST layer goes to HBM as the trunk FC's A operand, [k-chunk][128 boards][8 channels]: a board owns 16 bytes of
+        // every 128-byte line, so a store instruction costs 32 line accesses whatever its width -- that, not bandwidth, is what
+        // the drain takes. The pair's two boards sit next to each other there, so for this layer the threads change roles:
+        // each takes 32 channels of BOTH boards (reading the sibling board's accumulator and residual image too) and writes
+        // full 32-byte sectors with 256-bit stores -- half as many store instructions.
+        auto drain_pair = [&](auto HAS_RES) {
+          const int64_t board0 = pair * kBoards;
+          const bool both = board0 + 1 < p.batch;
+          uint8_t* g0 = p.fc_a + (((board0 >> 7) * p.n_kc + (int64_t)pos * (L.cout / 8)) * 128 + (board0 & 127)) * 16;
+          const uint32_t tmem_q = tmem_base + ((uint32_t)(q * 32) << 16) + par * 256u;
+          const uint32_t row_u = act_u + (uint32_t)(kHalo + m) * 16 + ((uint32_t)(has_res ? L.res : 0) ^ par) * kBufBytes;
+#pragma unroll 1
+          for (int c0 = (eb * kEpiSplit + eh) * 32; c0 < cout; c0 += 32 * kEpiSplit * kBoards) {
+            uint4 out[kBoards][4];
+#pragma unroll
+            for (int b = 0; b < kBoards; ++b) {
+              uint32_t r[32];
+              tmem_ld32(tmem_q + (uint32_t)b * 128u + (uint32_t)c0, r);
+              tmem_ld_wait();
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                const float4 ba = *reinterpret_cast<const float4*>(bias + c0 + i * 8), bb = *reinterpret_cast<const float4*>(bias + c0 + i * 8 + 4);
+                float v[8] = {__uint_as_float(r[i * 8 + 0]) + ba.x, __uint_as_float(r[i * 8 + 1]) + ba.y, __uint_as_float(r[i * 8 + 2]) + ba.z,
+                              __uint_as_float(r[i * 8 + 3]) + ba.w, __uint_as_float(r[i * 8 + 4]) + bb.x, __uint_as_float(r[i * 8 + 5]) + bb.y,
+                              __uint_as_float(r[i * 8 + 6]) + bb.z, __uint_as_float(r[i * 8 + 7]) + bb.w};
+                if constexpr (decltype(HAS_RES)::value)
+                  add8<FMT>(v, lds128(row_u + (uint32_t)b * 2 * kBufBytes + (uint32_t)(c0 / 8 + i) * kPlaneBytes));
+                out[b][i] = pack8_act<ACT, FMT>(v, keep);
+              }
+            }
+            if (inside) {
+#pragma unroll
+              for (int i = 0; i < 4; ++i) {
+                uint8_t* dst = g0 + (size_t)(c0 / 8 + i) * 2048;
+                if (both) stg256(dst, out[0][i], out[1][i]);
+                else *reinterpret_cast<uint4*>(dst) = out[0][i];  // the batch's last, odd board
+              }
+            }
+          }
+        };
         using std::false_type;
         using std::true_type;
-        if (has_res) {
+        if (kPairDrain && !to_smem) {
+          // the sibling board's last accumulator: its own barrier, completed once per pair (the per-layer one could be a
+          // phase further by the time a late warp looks at it)
+          ok = wait_bar(eb == 1 ? bar_last0 : bar_last1, last_phase, p.status, 8u);
+          if (!ok) break;
+          last_phase ^= 1u;
+          tc_fence_after();
+          if (has_res) drain_pair(true_type{});
+          else drain_pair(false_type{});
+        } else if (has_res) {
           if (to_smem) drain(true_type{}, true_type{});
           else drain(true_type{}, false_type{});
         } else {
@@ -565,7 +630,11 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
       if (AT_TOWER_OVERLAP) {
         // the sibling warp (other channel share, same rows) may still read this pair's residual image, which the next pair's
         // second layer overwrites: everyone finishes the drain first
-        if (!AT_DBG(64u)) asm volatile("bar.sync %0, %1;" ::"r"(1 + eb), "r"(kEpiWarps / kBoards * 32) : "memory");
+        // (with the pair drain every epilogue warp reads both boards' images: all sixteen warps meet)
+        if (!AT_DBG(64u)) {
+          if (kPairDrain) asm volatile("bar.sync 3, %0;" ::"n"(kEpiWarps * 32) : "memory");
+          else asm volatile("bar.sync %0, %1;" ::"r"(1 + eb), "r"(kEpiWarps / kBoards * 32) : "memory");
+        }
         par ^= 1u;
       }
     }
