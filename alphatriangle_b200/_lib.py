@@ -160,7 +160,7 @@ def load() -> C.CDLL:
 
 # include/at_b200_probe.h: the bring-up probes live in their own library (tests/test_gpu_probe.py, tools/mma_rate.py)
 PROBE_LIB_PATH = Path(__file__).resolve().parent / "libat_b200_probe.so"
-PROBE_EXPORTS = ("at_probe_last_error", "at_probe_umma", "at_probe_umma_ts", "at_probe_mma_rate")
+PROBE_EXPORTS = ("at_probe_last_error", "at_probe_umma", "at_probe_umma_ts", "at_probe_mma_rate", "at_probe_hog")
 _probe = None
 
 
@@ -176,6 +176,7 @@ def load_probe() -> C.CDLL:
         for name, args in (
             ("at_probe_umma_ts", [vp, vp, i64, i32, i32, i32, u32, u32, u32, u32, u32, u32, vp, vp, vp]),
             ("at_probe_mma_rate", [i32, i32, i32, i32, i32, vp, i32, vp, vp]),
+            ("at_probe_hog", [i32, C.c_longlong, vp, vp]),
             ("at_probe_umma", [vp, i64, vp, i64, i32, i32, u32, u32, u32, u32, u32, u32, u32, u32, i32, vp, vp, vp]),
         ):
             fn = getattr(lib, name)

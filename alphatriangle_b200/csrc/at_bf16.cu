@@ -68,6 +68,7 @@ constexpr int kTowerTmemCols = AT_TOWER_OVERLAP ? 512 : kBoards * 128;  // per b
 #define AT_TOWER_PAIR_DRAIN 1
 #endif
 constexpr bool kPairDrain = AT_TOWER_PAIR_DRAIN != 0 && AT_TOWER_OVERLAP != 0;  // last layer: 32 channels of both boards per thread
+constexpr int kPairQueue = 4;               // entries of the shared-memory queue of claimed board pairs
 constexpr int kMaxBars = 32;                 // mbarrier slots reserved in shared memory
 constexpr long long kTimeoutCycles = 2000000000LL;  // ~1 s: a wedged pipeline reports instead of hanging
 
@@ -81,7 +82,7 @@ constexpr long long kTimeoutCycles = 2000000000LL;  // ~1 s: a wedged pipeline r
 constexpr int kTlEvents = 256;
 __device__ unsigned long long g_timeline[32 * kTlEvents];
 #define AT_TL_DECL int tl_i = 0; bool tl_on = false;
-#define AT_TL_PAIR(pair) tl_on = (blockIdx.x == 0 && (pair) == (int64_t)3 * gridDim.x); tl_i = 0;
+#define AT_TL_PAIR(round) tl_on = (blockIdx.x == 0 && (round) == 3u); tl_i = 0;
 #define AT_TL(tag)                                                                                              \
   do {                                                                                                          \
     if (tl_on && (threadIdx.x & 31) == 0 && tl_i < kTlEvents) {                                                 \
@@ -91,7 +92,7 @@ __device__ unsigned long long g_timeline[32 * kTlEvents];
 #else
 #define AT_DBG(bits) false
 #define AT_TL_DECL
-#define AT_TL_PAIR(pair)
+#define AT_TL_PAIR(round)
 #define AT_TL(tag)
 #endif
 
@@ -120,12 +121,13 @@ struct TowerParams {
   int n_kc;                // L * C_last / 8
   int rows, cols;
   uint32_t* status;
+  int* pair_counter;  // null: board pairs by blockIdx stride; else handed out by this counter (zeroed before the launch)
   uint32_t debug;  // experiments build only (AT_TOWER_DEBUG): 1 no weight copies, 2 no MMAs, 4 no epilogue math, 8 no layer 0, 16 no weight ring
 };
 
 constexpr size_t tower_smem_bytes() {
   return (size_t)kStages * kStageBytes + (size_t)kBoards * 2 * kBufBytes + (size_t)kMaxLayers * 128 * 4 + 9 * 128 * 4 + 128 * 4 +
-         kMaxBars * 8 + 16;
+         kMaxBars * 8 + 16 + kPairQueue * 8;
 }
 
 __device__ __forceinline__ bool elect_one() {
@@ -162,6 +164,42 @@ __device__ __forceinline__ bool wait_bar(uint32_t bar, uint32_t parity, uint32_t
   atomicOr(status, code);
   return false;
 #endif
+}
+
+// ---- which board pair a CTA works on next ------------------------------------------------------------------------------
+// Both tower kernels are persistent, one CTA per SM. With pairs assigned by blockIdx stride every CTA must get its SM at
+// once: if anything else holds a few SMs (the NCCL kernel of a weight publication waiting for a slow rank), the CTAs left
+// over run as a second wave and the launch takes twice as long. So pairs are handed out by an atomic counter instead: a CTA
+// that starts late simply takes fewer. The weight producer, which runs ahead of everyone, claims a CTA's pairs one round
+// in advance and publishes them in a 4-entry shared-memory queue (round number in the high word, pair index or -1 = "no
+// more" in the low word); issuers and epilogue warps read entry `it` at their round `it` (the epilogue also entry it + 1,
+// for the hand-over).
+__device__ __forceinline__ void pairq_put(volatile unsigned long long* q, uint32_t it, int64_t pair) {
+  q[it & (kPairQueue - 1)] = ((unsigned long long)it << 32) | (uint32_t)(int32_t)pair;
+}
+__device__ __forceinline__ bool pairq_get(const volatile unsigned long long* q, uint32_t it, int64_t* pair, uint32_t* status) {
+  long long t0 = 0;
+  for (;;) {
+    const unsigned long long v = q[it & (kPairQueue - 1)];
+    if ((uint32_t)(v >> 32) == it) {
+      *pair = (int64_t)(int32_t)(uint32_t)v;
+      return true;
+    }
+    if (t0 == 0) t0 = clock64();
+    else if (clock64() - t0 > kTimeoutCycles) {
+      atomicOr(status, 16u);
+      return false;
+    }
+  }
+}
+// the producer's side: claim the next pair (or compute it, without a counter). The atomic's round trip to L2 is ~1 us, so
+// the claim is issued where the round starts and its result only used (pair_resolve, pairq_put) a few slabs later.
+__device__ __forceinline__ int64_t pair_claim_raw(int* counter, uint32_t it) {
+  return counter ? (int64_t)atomicAdd(counter, 1) : (int64_t)blockIdx.x + (int64_t)it * gridDim.x;
+}
+__device__ __forceinline__ int64_t pair_resolve(int64_t raw, int64_t n_pairs) { return raw < n_pairs ? raw : -1; }
+__device__ __forceinline__ int64_t pair_claim(int* counter, uint32_t it, int64_t n_pairs) {
+  return pair_resolve(pair_claim_raw(counter, it), n_pairs);
 }
 
 // ---- 16-bit operand formats (FMT_BF16 / FMT_F16, at_prepjobs.cuh). Activations are rounded to the operand format once,
@@ -285,6 +323,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   float* s_b0 = s_w0 + 9 * 128;                                       // [c0]
   uint64_t* bars = reinterpret_cast<uint64_t*>(s_b0 + 128);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + kMaxBars);
+  volatile unsigned long long* pairq = reinterpret_cast<volatile unsigned long long*>(tmem_slot + 4);
 
   const int tid = threadIdx.x, warp = tid / 32, lane = tid % 32;
   const uint32_t ring_u = smem_u32(ring), act_u = smem_u32(act);
@@ -300,6 +339,7 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   for (int i = tid; i < 9 * p.c0; i += kTowerThreads) s_w0[i] = p.w0[i];
   for (int i = tid; i < p.c0; i += kTowerThreads) s_b0[i] = p.b0[i];
   if (tid == 0) {
+    for (int i = 0; i < kPairQueue; ++i) pairq[i] = ~0ull;
     for (int i = 0; i < NS; ++i) {
       mbar_init(bar_full + 8 * i, 1);
       mbar_init(bar_empty + 8 * i, kBoards);  // both boards' issuers are done with the slab
@@ -323,7 +363,14 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
   const uint32_t tmem_base = *tmem_slot;
 
   const int64_t n_pairs = (p.batch + kBoards - 1) / kBoards;
-  const int64_t pair0 = blockIdx.x;
+  // the pair of round `it`: from the producer's queue (without the ring -- experiments only -- nobody runs ahead: by stride)
+  auto get_pair = [&](uint32_t it, int64_t* pair) -> bool {
+    if (!use_ring) {
+      *pair = pair_claim(nullptr, it, n_pairs);
+      return true;
+    }
+    return pairq_get(pairq, it, pair, p.status);
+  };
 
   if (warp == 0) {
     // ===== weight producer: one thread streams every layer's slabs through the ring, refilling each stage as soon as it
@@ -333,10 +380,19 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
       uint32_t stage = 0, phase = 0;
       bool ok = true;
       AT_TL_DECL
-      for (int64_t pair = pair0; pair < n_pairs && ok; pair += gridDim.x) {
-        AT_TL_PAIR(pair)
+      int64_t next = pair_claim(p.pair_counter, 0, n_pairs);
+      pairq_put(pairq, 0, next);
+      for (uint32_t it = 0; ok; ++it) {
+        const int64_t pair = next;
+        if (pair < 0) break;
+        const int64_t raw = pair_claim_raw(p.pair_counter, it + 1);  // one round ahead: the epilogue prepares the next pair during this one
+        AT_TL_PAIR(it)
         const uint8_t* src = p.wstream;
         for (int l = 0; l < p.n_layers && ok; ++l) {
+          if (l == 1 || p.n_layers == 1) {
+            next = pair_resolve(raw, n_pairs);
+            pairq_put(pairq, it + 1, next);
+          }
           AT_TL(100 + l);
           const uint32_t bytes = p.layers[l].slab_bytes;
           const int n_slabs = p.layers[l].n_slabs;
@@ -369,8 +425,11 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     uint32_t stage = 0, phase = 0, lphase = 0;
     bool ok = true;
     AT_TL_DECL
-    for (int64_t pair = pair0; pair < n_pairs && ok; pair += gridDim.x) {
-      AT_TL_PAIR(pair)
+    for (uint32_t it = 0; ok; ++it) {
+      int64_t pair;
+      ok = get_pair(it, &pair);
+      if (!ok || pair < 0) break;
+      AT_TL_PAIR(it)
       AT_TL(1);
       const uint32_t tmem_d = tmem_d0 + par * 256u;
       for (int l = 0; l < p.n_layers && ok; ++l) {
@@ -496,8 +555,12 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
     uint4 l0v[kL0Keep];
     AT_TL_DECL
     bool first = true;
-    for (int64_t pair = pair0; pair < n_pairs && ok; pair += gridDim.x) {
-      AT_TL_PAIR(pair)
+    for (uint32_t it = 0; ok; ++it) {
+      int64_t pair, next_pair;
+      ok = get_pair(it, &pair);
+      if (!ok || pair < 0) break;
+      next_pair = -1;
+      AT_TL_PAIR(it)
       AT_TL(1);
       const int64_t board = pair * kBoards + eb;
       const bool valid = board < p.batch;
@@ -517,8 +580,11 @@ __global__ void __launch_bounds__(kTowerThreads, 1) tower_kernel(const __grid_co
         // Overlap: while the last layer's MMAs run, work out the NEXT pair's layer 0 (registers); once they are done its
         // source image -- the pair's scratch buffer -- is free, so the next pair's first image goes there and its MMAs start
         // (on the other accumulator) while this pair's last accumulator is still being drained to HBM below.
-        const int64_t next_pair = pair + gridDim.x;
-        const bool hand_over = AT_TOWER_OVERLAP && l + 1 == p.n_layers && next_pair < n_pairs;
+        if (AT_TOWER_OVERLAP && l + 1 == p.n_layers) {  // published by the producer early in this round
+          ok = get_pair(it + 1, &next_pair);
+          if (!ok) break;
+        }
+        const bool hand_over = AT_TOWER_OVERLAP && l + 1 == p.n_layers && next_pair >= 0;
         const int64_t next_board = next_pair * kBoards + eb;
         if (hand_over && l0_in_regs) layer0(next_board, next_board < p.batch, l0v, true, 0);
         ok = wait_bar(my_acc, acc_phase, p.status, 8u);
@@ -762,7 +828,7 @@ __global__ void __launch_bounds__(kFcThreads, 2) fc_kernel(const __grid_constant
 
 constexpr size_t tower_tf_smem_bytes() {
   return (size_t)kTfStages * kStageBytes + (size_t)kBoards * 2 * kBufBytes + kMaskBytes + (size_t)kMaxLayers * 128 * 4 + 9 * 128 * 4 +
-         128 * 4 + (size_t)kXchFloats * 4 + (size_t)kTfBars * 8 + 16;
+         128 * 4 + (size_t)kXchFloats * 4 + (size_t)kTfBars * 8 + 16 + kPairQueue * 8;
 }
 
 }  // namespace
@@ -1166,6 +1232,9 @@ int bf16_trunk_partials(Bf16Path* b, const Plan& p, const float* folded, int slo
 #endif
   const int64_t n_pairs = (batch + kBoards - 1) / kBoards;
   const unsigned grid = (unsigned)(n_pairs < b->sms ? n_pairs : b->sms);
+  // more pairs than CTAs: hand them out by counter (status word 2), so that CTAs which get their SM late take fewer
+  tp.pair_counter = n_pairs > (int64_t)grid ? reinterpret_cast<int*>(b->status + 2) : nullptr;
+  if (tp.pair_counter) AT_CUDA_TRY(cudaMemsetAsync(tp.pair_counter, 0, sizeof(int), st));
   if (b->timing) AT_CUDA_TRY(cudaEventRecord(b->ev[0], st));
   if (b->tf) {
     TowerTfParams t = b->ttp;

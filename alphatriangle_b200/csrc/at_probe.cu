@@ -439,3 +439,24 @@ extern "C" int at_probe_mma_rate(int n, int mmas, int issuers, int copy, int epi
   AT_CUDA_TRY(cudaGetLastError());
   return AT_OK;
 }
+
+// ---- SM hog: `grid` CTAs that each take a whole SM (200 KB of dynamic shared memory) and spin for `cycles` -------------------
+namespace at {
+__global__ void hog_kernel(long long cycles, unsigned* d_sink) {
+  extern __shared__ unsigned hog_smem[];
+  const long long t0 = clock64();
+  unsigned v = 0;
+  while (clock64() - t0 < cycles) v += hog_smem[(v + threadIdx.x) & 1023];
+  if (v == 0xFFFFFFFFu) *d_sink = v;  // keeps the loop alive
+}
+}  // namespace at
+
+extern "C" int at_probe_hog(int grid, long long cycles, void* d_sink, void* stream) {
+  using namespace at;
+  if (grid < 1 || cycles < 0 || !d_sink) return fail(AT_E_INVALID, "at_probe_hog: bad argument");
+  const size_t smem = 200 * 1024;
+  AT_CUDA_TRY(cudaFuncSetAttribute(hog_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  hog_kernel<<<grid, 32, smem, static_cast<cudaStream_t>(stream)>>>(cycles, static_cast<unsigned*>(d_sink));
+  AT_CUDA_TRY(cudaGetLastError());
+  return AT_OK;
+}

@@ -35,6 +35,11 @@ int at_probe_umma_ts(const void* d_a_rows, const void* d_b_image, int64_t b_byte
 int at_probe_mma_rate(int n, int mmas, int issuers, int copy, int epi_warps, const void* d_src /* >= 32 KB */, int grid,
                       float* d_cycles /* [grid] */, void* stream);
 
+/* SM hog: `grid` CTAs, each taking a whole SM (200 KB of shared memory) and spinning for `cycles` SM cycles -- a stand-in for
+ * a collective's kernel that holds SMs while it waits for its peers (tools/contention.py: what a tower launch costs when it
+ * does not get every SM at once). No reference counterpart. d_sink: any 4 writable bytes. */
+int at_probe_hog(int grid, long long cycles, void* d_sink, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -160,6 +160,37 @@ def test_repeated_boards_agree_over_many_launches(case, fmt, golden_dir):
     assert int(bad) == 0
 
 
+@pytest.mark.parametrize("case", BF16_CASES)
+def test_results_do_not_depend_on_which_cta_takes_which_pair(case, golden_dir):
+    """Board pairs are handed out to the persistent CTAs by an atomic counter (so that a launch whose CTAs do not all get an SM
+    at once -- something else is running -- does not fall into a second wave). A second engine keeps a few SMs busy from a side
+    stream while the big batch is evaluated: the results must be the bits of the undisturbed evaluation."""
+    import alphatriangle_b200 as at
+    from golden_cases import case_configs, case_weights
+
+    _mc, _env, _seed, g = load_case(case, golden_dir)
+    nn = network(case, "f16", max_batch=8192)
+    mc_kwargs, env_kwargs, _ = case_configs(case)
+    hog = at.NeuralNetwork(at.ModelConfig(**mc_kwargs), at.EnvConfig(**env_kwargs), at.TrainConfig(), torch.device("cuda:0"),
+                           precision="f16", max_batch=64)
+    hog.set_weights(case_weights(case, hog.get_weights()))
+    base = g["packed"]
+    packed = torch.from_numpy(np.tile(base, (-(-8192 // base.shape[0]), 1))[:8192]).cuda()
+    small = torch.from_numpy(base[:32].copy()).cuda()
+    p0, v0 = nn.evaluate_packed(packed)
+    h0, _ = hog.evaluate_packed(small)
+    torch.cuda.synchronize()
+    side = torch.cuda.Stream()
+    with torch.cuda.stream(side):
+        for _ in range(400):
+            h1, _ = hog.evaluate_packed(small)
+    for _ in range(6):
+        p1, v1 = nn.evaluate_packed(packed)
+        assert torch.equal(p1, p0) and torch.equal(v1, v0)
+    torch.cuda.synchronize()
+    assert torch.equal(h1, h0)
+
+
 def test_bf16_through_the_drop_in_api(golden_dir):
     from golden_cases import case_states
 
