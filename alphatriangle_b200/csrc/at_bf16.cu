@@ -187,7 +187,7 @@ __device__ __forceinline__ bool pairq_get(const volatile unsigned long long* q, 
     }
     if (t0 == 0) t0 = clock64();
     else if (clock64() - t0 > kTimeoutCycles) {
-      atomicOr(status, 16u);
+      atomicOr(status, 128u);
       return false;
     }
   }

@@ -208,7 +208,7 @@ int at_engine_set_kernel_timing(at_engine* e, int on);
 int at_engine_kernel_ms(const at_engine* e, float* tower_ms, float* fc_ms);
 #define AT_FLAG_PIPELINE_TIMEOUT 0x80000000u /* a tcgen05 pipeline wait timed out; bits 8..15 say which: 1 weight producer (ring
                                               * stage), 2 issuer (operands), 4 issuer (weight slab), 8 epilogue (accumulator),
-                                              * 16 board-pair queue */
+                                              * 16/32/64 trunk FC (ring stage, slab, accumulator), 128 board-pair queue */
 int at_engine_action_dim(const at_engine* e);
 
 /* Test hook: the bf16 path up to and including the first shared FC layer
