@@ -68,14 +68,16 @@ class FlatWeights:
     # ---- header tail ------------------------------------------------------------------
     def write_header(self, version: int) -> None:
         """Sender side, before the collective: version word and the integer buffers, all device-side."""
-        with torch.no_grad():
-            self.header[0] = int(version)
-            self.header[1] = self.image_floats
-            for i, t in enumerate(self._ints):
-                self.header[HEADER_FIXED + i] = t.reshape(-1)[0].to(device=self.device, dtype=torch.int64)
+        with torch.no_grad():  # two small copies instead of one per word: publish() runs on the evaluating thread
+            self.header[:2].copy_(torch.tensor([int(version), self.image_floats], dtype=torch.int64), non_blocking=True)
+            if self._ints:
+                words = torch.stack([t.reshape(-1)[0] for t in self._ints])
+                self.header[HEADER_FIXED : HEADER_FIXED + len(self._ints)].copy_(words.to(device=self.device, dtype=torch.int64))
 
     def apply_header(self) -> None:
         """Receiver side, after the collective: integer buffers out of the tail, device-side (no host sync)."""
         with torch.no_grad():
-            for i, t in enumerate(self._ints):
-                t.copy_(self.header[HEADER_FIXED + i].to(t.device))
+            if self._ints:
+                words = self.header[HEADER_FIXED : HEADER_FIXED + len(self._ints)]
+                dsts = [t.reshape(-1)[0] if t.dim() else t for t in self._ints]
+                torch._foreach_copy_(dsts, list(words.to(dsts[0].device).unbind()))
