@@ -47,6 +47,9 @@ class Engine:
         self._h_policy = torch.empty((self.max_batch, self.action_dim), dtype=torch.float32, pin_memory=True)
         self._h_value = torch.empty((self.max_batch,), dtype=torch.float32, pin_memory=True)
         self._h_flags = torch.zeros((4,), dtype=torch.int32, pin_memory=True)
+        # evaluate_host is what a search calls with a few dozen leaves: its numpy views and ctypes pointers are made once
+        self._h_np = (self._h_states.numpy(), self._h_policy.numpy(), self._h_value.numpy(), self._h_flags.numpy())
+        self._h_ptrs = (_ptr(self._h_states), _ptr(self._h_policy), _ptr(self._h_value), _ptr(self._h_flags))
         self._slots: list = [None, None]  # pinned staging of the pipelined host calls, allocated on first use
         self._slot_batch = [0, 0]
         self._d_flags = torch.zeros((4,), dtype=torch.int32, device=self.device)
@@ -165,16 +168,16 @@ class Engine:
         b = int(packed.shape[0])
         if b > self.max_batch:
             raise ValueError(f"batch {b} exceeds max_batch {self.max_batch}")
-        src = packed if isinstance(packed, torch.Tensor) else torch.from_numpy(np.ascontiguousarray(packed))
-        self._h_states[:b].copy_(src)
-        _lib.check(
-            self.lib.at_engine_evaluate_host(
-                self.handle, precision, _ptr(self._h_states), b, _ptr(self._h_policy), _ptr(self._h_value), _ptr(self._h_flags),
-                _stream_ptr(self.device),
-            ),
-            "at_engine_evaluate_host",
-        )
-        return self._h_policy[:b].numpy(), self._h_value[:b].numpy(), int(self._h_flags[0].item())
+        states_np, policy_np, value_np, flags_np = self._h_np
+        if isinstance(packed, torch.Tensor):
+            self._h_states[:b].copy_(packed)
+        else:
+            states_np[:b] = packed
+        p_states, p_policy, p_value, p_flags = self._h_ptrs
+        rc = self.lib.at_engine_evaluate_host(self.handle, precision, p_states, b, p_policy, p_value, p_flags, _stream_ptr(self.device))
+        if rc != _lib.AT_OK:
+            _lib.check(rc, "at_engine_evaluate_host")
+        return policy_np[:b], value_np[:b], int(flags_np[0])
 
     # ---- two batches in flight (at_engine_submit_host / at_engine_wait_host) ----
     def _slot_buffers(self, slot: int):
